@@ -1,0 +1,203 @@
+// gpx_acq_reduce / gpx_argmax_finalize: mixture moments over the posterior
+// samples, output-transform reversal, analytic EI / UCB / UE and a deterministic
+// first-max argmax.  Replaces GPSample.mu/sd (RNG-free limit, gpax/gp.py:76-90),
+// UpperConfidenceBound._analytic (gpax/acquisition.py:260-266),
+// ExpectedImprovement._analytic (gpax/acquisition.py:291-298) and the
+// vals.argmax() of gpax/acquisition.py:214.
+//
+// HBM-read bound: 16*S*M bytes in, <= 24*M bytes out.  One thread owns one
+// candidate and walks the samples in the fixed order s = 0..S-1 (so the result
+// does not depend on how candidates are sharded over GPUs); a warp reads 256
+// contiguous bytes of mu and of var per sample, 8 samples in flight.
+#include "common.cuh"
+
+namespace gpx {
+
+constexpr int A_THREADS = 256;
+
+struct Best {
+    double v;
+    int64_t i;
+};
+// jnp.argmax ordering: NaN is maximal, ties go to the lowest index
+__device__ __forceinline__ bool better(const Best &a, const Best &b) {
+    const bool an = isnan(a.v), bn = isnan(b.v);
+    if (an != bn) return an;
+    if (an && bn) return a.i < b.i;
+    if (a.v != b.v) return a.v > b.v;
+    return a.i < b.i;
+}
+__device__ __forceinline__ Best best_shfl(Best b, int o) {
+    Best r;
+    r.v = __shfl_xor_sync(0xffffffffu, b.v, o);
+    r.i = __shfl_xor_sync(0xffffffffu, (long long)b.i, o);
+    return r;
+}
+__device__ __forceinline__ Best block_best(Best b, Best *sbuf) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        Best r = best_shfl(b, o);
+        if (better(r, b)) b = r;
+    }
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (lane == 0) sbuf[warp] = b;
+    __syncthreads();
+    if (warp == 0) {
+        const int nw = blockDim.x >> 5;
+        Best c = sbuf[lane < nw ? lane : 0];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            Best r = best_shfl(c, o);
+            if (better(r, c)) c = r;
+        }
+        b = c;
+    }
+    return b;   // valid in warp 0
+}
+
+// jax.scipy.special.ndtr as used by numpyro Normal.cdf (gpax/acquisition.py:295-296)
+__device__ __forceinline__ double ndtr_jax(double x) {
+    const double rh = 0.7071067811865476;   // sqrt(0.5)
+    double w = x * rh, z = fabs(w);
+    double y;
+    if (z < rh) y = 1.0 + erf(w);
+    else if (w > 0.0) y = 2.0 - erfc(z);
+    else y = erfc(z);
+    return 0.5 * y;
+}
+
+__device__ __forceinline__ double acq_value(int acq, double mu, double sd, double coef,
+                                            double y_max) {
+    if (acq == GPX_ACQ_EI) {
+        double u = (mu - y_max) / sd;
+        double cdf = ndtr_jax(u);
+        double pdf = exp(-0.5 * u * u - 0.9189385332046727 /* log(sqrt(2 pi)) */);
+        return sd * pdf + (mu - y_max) * cdf;
+    }
+    if (acq == GPX_ACQ_UCB) return mu + coef * sd;
+    if (acq == GPX_ACQ_UE) return sd;
+    return mu;
+}
+
+__global__ void __launch_bounds__(A_THREADS)
+acq_reduce_kernel(int64_t S, int64_t M, const double *__restrict__ mu,
+                  const double *__restrict__ var, int acq, double coef, double y_max,
+                  double mu_scale, double mu_shift, double sd_scale, int64_t m_offset,
+                  double *__restrict__ out_mu, double *__restrict__ out_sd,
+                  double *__restrict__ out_acq, double *__restrict__ part_val,
+                  int64_t *__restrict__ part_idx) {
+    __shared__ Best sbuf[A_THREADS / 32];
+    const int64_t j = (int64_t)blockIdx.x * A_THREADS + threadIdx.x;
+    Best mine;
+    mine.v = -INFINITY;
+    mine.i = INT64_MAX;
+    if (j < M) {
+        double mbar, vbar;
+        if (S == 1) {
+            mbar = mu[j];
+            vbar = var[j];
+        } else {
+            double a = 0.0, b = 0.0;
+            int64_t s = 0;
+            for (; s + 8 <= S; s += 8) {
+                double m_[8], v_[8];
+#pragma unroll
+                for (int q = 0; q < 8; ++q) {
+                    m_[q] = mu[(s + q) * M + j];
+                    v_[q] = var[(s + q) * M + j];
+                }
+#pragma unroll
+                for (int q = 0; q < 8; ++q) {
+                    a = a + m_[q];
+                    b = b + (v_[q] + m_[q] * m_[q]);
+                }
+            }
+            for (; s < S; ++s) {
+                double m1 = mu[s * M + j], v1 = var[s * M + j];
+                a = a + m1;
+                b = b + (v1 + m1 * m1);
+            }
+            mbar = a / (double)S;
+            vbar = b / (double)S - mbar * mbar;
+        }
+        const double mu_u = mbar * mu_scale + mu_shift;
+        const double sd_u = sqrt(vbar) * sd_scale;
+        const double val = acq_value(acq, mu_u, sd_u, coef, y_max);
+        if (out_mu) out_mu[j] = mu_u;
+        if (out_sd) out_sd[j] = sd_u;
+        if (out_acq) out_acq[j] = val;
+        mine.v = val;
+        mine.i = m_offset + j;
+    }
+    Best b = block_best(mine, sbuf);
+    if (threadIdx.x == 0) {
+        part_val[blockIdx.x] = b.v;
+        part_idx[blockIdx.x] = b.i;
+    }
+}
+
+__global__ void __launch_bounds__(1024)
+argmax_finalize_kernel(int64_t P, const double *__restrict__ part_val,
+                       const int64_t *__restrict__ part_idx, double *__restrict__ best_val,
+                       int64_t *__restrict__ best_idx) {
+    __shared__ Best sbuf[32];
+    Best mine;
+    mine.v = -INFINITY;
+    mine.i = INT64_MAX;
+    for (int64_t k = threadIdx.x; k < P; k += blockDim.x) {
+        Best c;
+        c.v = part_val[k];
+        c.i = part_idx[k];
+        if (better(c, mine)) mine = c;
+    }
+    Best b = block_best(mine, sbuf);
+    if (threadIdx.x == 0) {
+        if (best_val) *best_val = b.v;
+        if (best_idx) *best_idx = b.i;
+    }
+}
+
+}  // namespace gpx
+
+extern "C" int64_t gpx_acq_parts(int64_t M) { return (M + gpx::A_THREADS - 1) / gpx::A_THREADS; }
+
+extern "C" int gpx_acq_reduce(int64_t S, int64_t M, const double *mu, const double *var,
+                              int32_t acq, double beta, double y_max, double mu_scale,
+                              double mu_shift, double sd_scale, int64_t m_offset, double *out_mu,
+                              double *out_sd, double *out_acq, double *part_val,
+                              int64_t *part_idx, void *stream) {
+    using namespace gpx;
+    GPX_ARG_CHECK(S >= 1, 1);
+    GPX_ARG_CHECK(M >= 0, 2);
+    GPX_ARG_CHECK(mu != nullptr || M == 0, 3);
+    GPX_ARG_CHECK(var != nullptr || M == 0, 4);
+    GPX_ARG_CHECK(acq >= GPX_ACQ_EI && acq <= GPX_ACQ_MEAN, 5);
+    GPX_ARG_CHECK(!(acq == GPX_ACQ_UCB) || beta >= 0.0, 6);
+    GPX_ARG_CHECK(part_val != nullptr && part_idx != nullptr, 15);
+    if (M == 0) return 0;
+    // gpax/acquisition.py:261-266: beta = inf -> sd, beta = 0 -> mu
+    double coef = 0.0;
+    if (acq == GPX_ACQ_UCB) {
+        if (isinf(beta)) acq = GPX_ACQ_UE;
+        else if (beta == 0.0) acq = GPX_ACQ_MEAN;
+        else coef = sqrt(beta + 1e-12);
+    }
+    unsigned grid = (unsigned)gpx_acq_parts(M);
+    acq_reduce_kernel<<<grid, A_THREADS, 0, (cudaStream_t)stream>>>(
+        S, M, mu, var, acq, coef, y_max, mu_scale, mu_shift, sd_scale, m_offset, out_mu, out_sd,
+        out_acq, part_val, part_idx);
+    GPX_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int gpx_argmax_finalize(int64_t P, const double *part_val, const int64_t *part_idx,
+                                   double *best_val, int64_t *best_idx, void *stream) {
+    using namespace gpx;
+    GPX_ARG_CHECK(P >= 1, 1);
+    GPX_ARG_CHECK(part_val != nullptr, 2);
+    GPX_ARG_CHECK(part_idx != nullptr, 3);
+    argmax_finalize_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(P, part_val, part_idx, best_val,
+                                                                 best_idx);
+    GPX_LAUNCH_CHECK();
+    return 0;
+}

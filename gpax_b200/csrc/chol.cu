@@ -1,0 +1,274 @@
+// Batched blocked Cholesky (gpx_potrf_batched) and triangular inverse
+// (gpx_trtri_batched) in FP64 with the block updates on DMMA tensor cores.
+// Replaces cho_factor (gpax/gp.py:296) / numpyro's cholesky (gpax/gp.py:147-151).
+//
+// Block size NB = 128.  Per block step p three batched launches:
+//   update : A(i,j) -= L(i,K) L(j,K)^T        (tile_gemm NT, DMMA)
+//   diag   : L(p,p) = chol(A(p,p)), Dinv(p) = L(p,p)^-1   (one CTA per matrix, smem)
+//   trsm   : L(i,p) = A(i,p) Dinv(p)^T        (tile_gemm NT, DMMA)
+// Two schedules share these kernels: LEFT-looking (deep-K update of block column
+// p only; each tile is read and written once -- used when S gives enough
+// parallelism) and RIGHT-looking (rank-NB update of the whole trailing matrix --
+// used for few large matrices, e.g. n = 16384, S = 1).
+#include "mma_tile.cuh"
+
+namespace gpx {
+
+constexpr int NB = GPX_NB;
+constexpr int DLD = NB + 1;  // odd leading dimension: conflict-free row & column walks
+constexpr size_t DIAG_SMEM = (size_t)(NB * DLD + NB) * sizeof(double);
+
+// ---------------------------------------------------------------------------
+// diag kernel: Cholesky + inverse of one NB x NB diagonal block in shared memory
+// ---------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+diag_kernel(int64_t n, int p, double *__restrict__ A, int64_t lda, double *__restrict__ dinv,
+            int32_t *__restrict__ info) {
+    extern __shared__ double sm[];
+    double *a = sm;               // [NB][DLD]
+    double *col = sm + NB * DLD;  // [NB]
+    const int64_t s = blockIdx.x;
+    const int T = (int)((n + NB - 1) / NB);
+    const int64_t r0 = (int64_t)p * NB;
+    const int nbe = (int)((n - r0 < NB) ? (n - r0) : NB);  // effective size
+    double *Ab = A + (size_t)s * n * lda + r0 * lda + r0;
+    const int t = threadIdx.x;
+
+    // load lower triangle; pad with identity
+    for (int e = t; e < NB * NB; e += 256) {
+        int i = e / NB, j = e % NB;
+        double v = (i == j) ? 1.0 : 0.0;
+        if (i < nbe && j <= i) v = Ab[(int64_t)i * lda + j];
+        a[i * DLD + j] = v;
+    }
+    __syncthreads();
+
+    // left-looking column Cholesky; thread pair (i, h) splits the k range by parity
+    const int i = t >> 1, h = t & 1;
+    int bad = 0;
+    for (int j = 0; j < nbe; ++j) {
+        double acc = 0.0;
+        if (i >= j) {
+            const double *ri = a + i * DLD, *rj = a + j * DLD;
+            for (int k = h; k < j; k += 2) acc = fma(ri[k], rj[k], acc);
+        }
+        acc += __shfl_xor_sync(0xffffffffu, acc, 1);
+        if (i >= j && h == 0) a[i * DLD + j] -= acc;
+        __syncthreads();
+        double djj = a[j * DLD + j];
+        if (!(djj > 0.0) && bad == 0) bad = j + 1;
+        double dj = sqrt(djj);
+        __syncthreads();
+        if (h == 0) {
+            if (i == j) a[i * DLD + j] = dj;
+            else if (i > j) a[i * DLD + j] = a[i * DLD + j] / dj;
+        }
+        __syncthreads();
+    }
+    if (t == 0 && bad && info) {
+        // LAPACK convention: order of the first non-positive leading minor
+        atomicCAS(&info[s], 0, (int32_t)(r0 + bad));
+    }
+    // write L block (zeros above the diagonal)
+    for (int e = t; e < nbe * nbe; e += 256) {
+        int ii = e / nbe, jj = e % nbe;
+        Ab[(int64_t)ii * lda + jj] = a[ii * DLD + jj];
+    }
+    __syncthreads();
+
+    // in-place inverse of the lower-triangular block, last column first
+    // (column j of X from the already inverted trailing block):
+    //   X[j][j] = 1/L[j][j];  X[i][j] = -X[j][j] * sum_{k=j+1..i} X[i][k] L[k][j]
+    for (int j = NB - 1; j >= 0; --j) {
+        if (t < NB) col[t] = a[t * DLD + j];
+        __syncthreads();
+        double xjj = 1.0 / col[j];
+        double acc = 0.0;
+        if (i > j) {
+            const double *ri = a + i * DLD;
+            for (int k = j + 1 + h; k <= i; k += 2) acc = fma(ri[k], col[k], acc);
+        }
+        acc += __shfl_xor_sync(0xffffffffu, acc, 1);
+        __syncthreads();
+        if (h == 0) {
+            if (i == j) a[i * DLD + j] = xjj;
+            else if (i > j) a[i * DLD + j] = -xjj * acc;
+        }
+        __syncthreads();
+    }
+    double *Db = dinv + ((size_t)s * T + p) * NB * NB;
+    for (int e = t; e < NB * NB; e += 256) {
+        int ii = e / NB, jj = e % NB;
+        Db[e] = a[ii * DLD + jj];
+    }
+}
+
+// ---------------------------------------------------------------------------
+// tile kernels (one CTA = one 128x128 tile; blockIdx.y = sample)
+// ---------------------------------------------------------------------------
+enum { OP_SYRK_LEFT = 0, OP_SYRK_RIGHT = 1, OP_TRSM = 2, OP_TRTRI_ACC = 3, OP_TRTRI_FIN = 4 };
+
+template <int OP>
+__global__ void __launch_bounds__(T_THREADS, 1)
+tile_kernel(int64_t n, int p, double *__restrict__ A, int64_t lda, const double *__restrict__ L,
+            int64_t ldl, const double *__restrict__ dinv) {
+    extern __shared__ __align__(16) double smem[];
+    const int64_t s = blockIdx.y;
+    const int T = (int)((n + NB - 1) / NB);
+    double *As = A + (size_t)s * n * lda;
+    const double *Ls = L ? L + (size_t)s * n * ldl : nullptr;
+    double acc[T_MF][T_NF][2];
+#pragma unroll
+    for (int mi = 0; mi < T_MF; ++mi)
+#pragma unroll
+        for (int ni = 0; ni < T_NF; ++ni) acc[mi][ni][0] = acc[mi][ni][1] = 0.0;
+
+    if (OP == OP_SYRK_LEFT) {
+        // tile (i, p), i = p + blockIdx.x;  K = [0, p*NB)
+        const int64_t i = p + blockIdx.x;
+        Operand a{As, lda, i * NB, 0, n, n};
+        Operand b{As, lda, (int64_t)p * NB, 0, n, n};
+        tile_gemm<false>(smem, a, b, (int64_t)p * NB, acc);
+        tile_store(As, lda, i * NB, (int64_t)p * NB, n, n, -1.0, true, acc);
+    } else if (OP == OP_SYRK_RIGHT) {
+        // tile (i, j), p < j <= i < T from a triangular enumeration; K = block p
+        const int64_t id = blockIdx.x;
+        int64_t aa = (int64_t)((sqrt(8.0 * (double)id + 1.0) - 1.0) * 0.5);
+        while (aa * (aa + 1) / 2 > id) --aa;
+        while ((aa + 1) * (aa + 2) / 2 <= id) ++aa;
+        const int64_t bb = id - aa * (aa + 1) / 2;
+        const int64_t i = p + 1 + aa, j = p + 1 + bb;
+        Operand a{As, lda, i * NB, (int64_t)p * NB, n, n};
+        Operand b{As, lda, j * NB, (int64_t)p * NB, n, n};
+        tile_gemm<false>(smem, a, b, NB, acc);
+        tile_store(As, lda, i * NB, j * NB, n, n, -1.0, true, acc);
+    } else if (OP == OP_TRSM) {
+        // tile (i, p), i = p + 1 + blockIdx.x:  A(i,p) <- A(i,p) * Dinv(p)^T
+        const int64_t i = p + 1 + blockIdx.x;
+        const double *D = dinv + ((size_t)s * T + p) * NB * NB;
+        Operand a{As, lda, i * NB, (int64_t)p * NB, n, n};
+        Operand b{D, NB, 0, 0, NB, NB};
+        tile_gemm<false>(smem, a, b, NB, acc);
+        tile_store(As, lda, i * NB, (int64_t)p * NB, n, n, 1.0, false, acc);
+    } else if (OP == OP_TRTRI_ACC) {
+        // W(p, j) = sum_{k=j..p-1} L(p,k) W(k,j), j = blockIdx.x  (A is W here)
+        const int64_t j = blockIdx.x;
+        Operand a{Ls, ldl, (int64_t)p * NB, j * NB, n, n};
+        Operand b{As, lda, j * NB, j * NB, n, n};
+        tile_gemm<true>(smem, a, b, (int64_t)(p - j) * NB, acc);
+        tile_store(As, lda, (int64_t)p * NB, j * NB, n, n, 1.0, false, acc);
+    } else {
+        // W(p, j) <- -Dinv(p) * W(p, j), j = blockIdx.x
+        const int64_t j = blockIdx.x;
+        const double *D = dinv + ((size_t)s * T + p) * NB * NB;
+        Operand a{D, NB, 0, 0, NB, NB};
+        Operand b{As, lda, (int64_t)p * NB, j * NB, n, n};
+        tile_gemm<true>(smem, a, b, NB, acc);
+        tile_store(As, lda, (int64_t)p * NB, j * NB, n, n, -1.0, false, acc);
+    }
+}
+
+// copy Dinv blocks onto the diagonal of W
+__global__ void __launch_bounds__(256)
+trtri_diag_copy_kernel(int64_t n, const double *__restrict__ dinv, double *__restrict__ W,
+                       int64_t ldw) {
+    const int64_t s = blockIdx.y;
+    const int p = blockIdx.x;
+    const int T = (int)((n + NB - 1) / NB);
+    const double *D = dinv + ((size_t)s * T + p) * NB * NB;
+    double *Wb = W + (size_t)s * n * ldw;
+    const int64_t r0 = (int64_t)p * NB;
+    for (int e = threadIdx.x; e < NB * NB; e += 256) {
+        int i = e / NB, j = e % NB;
+        if (r0 + i < n && r0 + j < n) Wb[(r0 + i) * ldw + r0 + j] = D[e];
+    }
+}
+
+static int set_attrs_once() {
+    static int done = 0;
+    if (done) return 0;
+    cudaError_t e;
+#define GPX_SET(K, BYTES)                                                                  \
+    e = cudaFuncSetAttribute(K, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(BYTES)); \
+    if (e != cudaSuccess) return (int)e;
+    GPX_SET(diag_kernel, DIAG_SMEM);
+    GPX_SET(tile_kernel<OP_SYRK_LEFT>, T_SMEM_BYTES);
+    GPX_SET(tile_kernel<OP_SYRK_RIGHT>, T_SMEM_BYTES);
+    GPX_SET(tile_kernel<OP_TRSM>, T_SMEM_BYTES);
+    GPX_SET(tile_kernel<OP_TRTRI_ACC>, T_SMEM_BYTES);
+    GPX_SET(tile_kernel<OP_TRTRI_FIN>, T_SMEM_BYTES);
+#undef GPX_SET
+    done = 1;
+    return 0;
+}
+
+}  // namespace gpx
+
+extern "C" size_t gpx_dinv_bytes(int64_t S, int64_t n) {
+    int64_t T = (n + GPX_NB - 1) / GPX_NB;
+    return (size_t)S * T * GPX_NB * GPX_NB * sizeof(double);
+}
+
+extern "C" int gpx_potrf_batched(int64_t S, int64_t n, double *A, int64_t lda, double *dinv,
+                                 int32_t *info, void *stream) {
+    using namespace gpx;
+    GPX_ARG_CHECK(S >= 0 && S <= 65535, 1);
+    GPX_ARG_CHECK(n >= 0, 2);
+    GPX_ARG_CHECK(A != nullptr || S * n == 0, 3);
+    GPX_ARG_CHECK(lda >= n && (lda % 2 == 0), 4);
+    GPX_ARG_CHECK(dinv != nullptr || S * n == 0, 5);
+    if (S == 0 || n == 0) return 0;
+    int rc = set_attrs_once();
+    if (rc) { set_error("cudaFuncSetAttribute failed: %d", rc); return rc; }
+    cudaStream_t st = (cudaStream_t)stream;
+    if (info) cudaMemsetAsync(info, 0, sizeof(int32_t) * S, st);
+    const int T = (int)((n + NB - 1) / NB);
+    // schedule: left-looking when the batch alone fills the machine
+    const bool left = (S * (int64_t)((T + 1) / 2) >= 296);
+    for (int p = 0; p < T; ++p) {
+        if (left && p > 0) {
+            dim3 g((unsigned)(T - p), (unsigned)S);
+            tile_kernel<OP_SYRK_LEFT><<<g, T_THREADS, T_SMEM_BYTES, st>>>(n, p, A, lda, nullptr, 0, dinv);
+        }
+        diag_kernel<<<(unsigned)S, 256, DIAG_SMEM, st>>>(n, p, A, lda, dinv, info);
+        if (p + 1 < T) {
+            dim3 g((unsigned)(T - p - 1), (unsigned)S);
+            tile_kernel<OP_TRSM><<<g, T_THREADS, T_SMEM_BYTES, st>>>(n, p, A, lda, nullptr, 0, dinv);
+            if (!left) {
+                int64_t tr = T - p - 1;
+                dim3 g2((unsigned)(tr * (tr + 1) / 2), (unsigned)S);
+                tile_kernel<OP_SYRK_RIGHT><<<g2, T_THREADS, T_SMEM_BYTES, st>>>(n, p, A, lda, nullptr, 0, dinv);
+            }
+        }
+    }
+    GPX_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int gpx_trtri_batched(int64_t S, int64_t n, const double *L, int64_t ldl,
+                                 const double *dinv, double *W, int64_t ldw, void *stream) {
+    using namespace gpx;
+    GPX_ARG_CHECK(S >= 0 && S <= 65535, 1);
+    GPX_ARG_CHECK(n >= 0, 2);
+    GPX_ARG_CHECK(L != nullptr || S * n == 0, 3);
+    GPX_ARG_CHECK(ldl >= n && (ldl % 2 == 0), 4);
+    GPX_ARG_CHECK(dinv != nullptr || S * n == 0, 5);
+    GPX_ARG_CHECK(W != nullptr || S * n == 0, 6);
+    GPX_ARG_CHECK(ldw >= n && (ldw % 2 == 0), 7);
+    if (S == 0 || n == 0) return 0;
+    int rc = set_attrs_once();
+    if (rc) { set_error("cudaFuncSetAttribute failed: %d", rc); return rc; }
+    cudaStream_t st = (cudaStream_t)stream;
+    const int T = (int)((n + NB - 1) / NB);
+    {
+        dim3 g((unsigned)T, (unsigned)S);
+        trtri_diag_copy_kernel<<<g, 256, 0, st>>>(n, dinv, W, ldw);
+    }
+    for (int p = 1; p < T; ++p) {
+        dim3 g((unsigned)p, (unsigned)S);
+        tile_kernel<OP_TRTRI_ACC><<<g, T_THREADS, T_SMEM_BYTES, st>>>(n, p, W, ldw, L, ldl, dinv);
+        tile_kernel<OP_TRTRI_FIN><<<g, T_THREADS, T_SMEM_BYTES, st>>>(n, p, W, ldw, L, ldl, dinv);
+    }
+    GPX_LAUNCH_CHECK();
+    return 0;
+}

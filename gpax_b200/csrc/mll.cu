@@ -1,0 +1,148 @@
+// gpx_mll: z = L^-1 r, alpha = L^-T z and the multivariate-normal log density
+// (numpyro MultivariateNormal.log_prob as used at gpax/gp.py:147-151; the alpha
+// solve is cho_solve(K, y - m) of gpax/gp.py:300).
+//
+// One CTA per posterior sample; z/alpha live in shared memory (n doubles), L is
+// streamed once per direction with 16-byte loads (HBM bound: 8*n^2 bytes per
+// sample in total).  Diagonal blocks are applied through the Dinv blocks left by
+// gpx_potrf_batched, so there is no scalar substitution chain.
+#include "common.cuh"
+
+namespace gpx {
+
+constexpr int MNB = GPX_NB;
+constexpr int MTHREADS = 256;
+
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+__global__ void __launch_bounds__(MTHREADS)
+mll_kernel(int64_t n, const double *__restrict__ L, int64_t ldl, const double *__restrict__ dinv,
+           const double *__restrict__ resid, int64_t resid_stride, double *__restrict__ alpha,
+           double *__restrict__ mll) {
+    extern __shared__ double sm[];
+    double *z = sm;                 // [n rounded up to MNB]
+    const int T = (int)((n + MNB - 1) / MNB);
+    double *tmp = sm + (size_t)T * MNB;   // [MNB]
+    double *tmp2 = tmp + MNB;             // [MNB]
+    double *red = tmp2 + MNB;             // [MTHREADS]
+    const int64_t s = blockIdx.x;
+    const double *Ls = L + (size_t)s * n * ldl;
+    const double *Ds = dinv + (size_t)s * T * MNB * MNB;
+    const double *r = resid + (size_t)s * resid_stride;
+    const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
+
+    double logdet = 0.0;
+    // ---------------- forward: z = L^-1 r ----------------
+    for (int b = 0; b < T; ++b) {
+        const int64_t r0 = (int64_t)b * MNB;
+        const int64_t K = r0;
+        // tmp[i] = r[r0+i] - L[r0+i, :K] . z[:K]   (warp per row, 16 rows per warp)
+        for (int ii = 0; ii < MNB / 8; ++ii) {
+            const int i = warp * (MNB / 8) + ii;
+            const int64_t gr = r0 + i;
+            double acc = 0.0;
+            if (gr < n) {
+                const double *row = Ls + gr * ldl;
+                for (int64_t k = lane * 2; k < K; k += 64) {
+                    double2 v = *reinterpret_cast<const double2 *>(row + k);
+                    acc = fma(v.x, z[k], acc);
+                    acc = fma(v.y, z[k + 1], acc);
+                }
+            }
+            acc = warp_sum(acc);
+            if (lane == 0) tmp[i] = (gr < n) ? (r[gr] - acc) : 0.0;
+        }
+        __syncthreads();
+        // z_b = Dinv_b * tmp  (lower triangular 128x128)
+        const double *D = Ds + (size_t)b * MNB * MNB;
+        for (int ii = 0; ii < MNB / 8; ++ii) {
+            const int i = warp * (MNB / 8) + ii;
+            double acc = 0.0;
+            for (int k = lane; k <= i; k += 32) acc = fma(D[i * MNB + k], tmp[k], acc);
+            acc = warp_sum(acc);
+            if (lane == 0) z[r0 + i] = (r0 + i < n) ? acc : 0.0;
+        }
+        if (t < MNB && r0 + t < n) logdet += log(Ls[(r0 + t) * ldl + r0 + t]);
+        __syncthreads();
+    }
+    // z.z and log det: fixed-order block reduction
+    double zz = 0.0;
+    for (int64_t k = t; k < n; k += MTHREADS) zz = fma(z[k], z[k], zz);
+    red[t] = zz;
+    __syncthreads();
+    for (int o = MTHREADS / 2; o > 0; o >>= 1) {
+        if (t < o) red[t] += red[t + o];
+        __syncthreads();
+    }
+    zz = red[0];
+    __syncthreads();
+    red[t] = logdet;
+    __syncthreads();
+    for (int o = MTHREADS / 2; o > 0; o >>= 1) {
+        if (t < o) red[t] += red[t + o];
+        __syncthreads();
+    }
+    if (t == 0 && mll)
+        mll[s] = -0.5 * zz - red[0] - 0.5 * (double)n * 1.8378770664093453 /* log(2 pi) */;
+    __syncthreads();
+    if (!alpha) return;
+
+    // ---------------- backward: alpha = L^-T z (in place in z) ----------------
+    const int c = t & (MNB - 1), half = t >> 7;   // 2 row-groups x 128 columns
+    for (int b = T - 1; b >= 0; --b) {
+        const int64_t c0 = (int64_t)b * MNB;
+        double acc = 0.0;
+        if (c0 + c < n) {
+            for (int64_t rr = c0 + MNB + half; rr < n; rr += 2)
+                acc = fma(Ls[rr * ldl + c0 + c], z[rr], acc);
+        }
+        if (half == 1) tmp2[c] = acc;
+        __syncthreads();
+        if (half == 0) tmp[c] = z[c0 + c] - (acc + tmp2[c]);
+        __syncthreads();
+        // alpha_b = Dinv_b^T * tmp : alpha_i = sum_{k >= i} D[k][i] tmp[k]
+        const double *D = Ds + (size_t)b * MNB * MNB;
+        double a2 = 0.0;
+        for (int k = c + half; k < MNB; k += 2) {
+            if (k >= c) a2 = fma(D[k * MNB + c], tmp[k], a2);
+        }
+        if (half == 1) tmp2[c] = a2;
+        __syncthreads();
+        if (half == 0) z[c0 + c] = (c0 + c < n) ? (a2 + tmp2[c]) : 0.0;
+        __syncthreads();
+    }
+    for (int64_t k = t; k < n; k += MTHREADS) alpha[(size_t)s * n + k] = z[k];
+}
+
+}  // namespace gpx
+
+extern "C" int gpx_mll(int64_t S, int64_t n, const double *L, int64_t ldl, const double *dinv,
+                       const double *resid, int64_t resid_stride, double *alpha, double *mll,
+                       void *stream) {
+    using namespace gpx;
+    GPX_ARG_CHECK(S >= 0, 1);
+    GPX_ARG_CHECK(n >= 0, 2);
+    GPX_ARG_CHECK(L != nullptr || S * n == 0, 3);
+    GPX_ARG_CHECK(ldl >= n && (ldl % 2 == 0), 4);
+    GPX_ARG_CHECK(dinv != nullptr || S * n == 0, 5);
+    GPX_ARG_CHECK(resid != nullptr || S * n == 0, 6);
+    if (S == 0 || n == 0) return 0;
+    const int64_t T = (n + MNB - 1) / MNB;
+    size_t smem = (size_t)(T * MNB + 2 * MNB + MTHREADS) * sizeof(double);
+    GPX_ARG_CHECK(smem <= 227 * 1024, 2);   // n <= ~28k for the single-CTA solve
+    static size_t configured = 0;
+    if (smem > configured) {
+        cudaError_t e = cudaFuncSetAttribute(mll_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             (int)smem);
+        if (e != cudaSuccess) { set_error("gpx_mll: smem attribute failed (%d)", (int)e); return (int)e; }
+        configured = smem;
+    }
+    mll_kernel<<<(unsigned)S, MTHREADS, smem, (cudaStream_t)stream>>>(n, L, ldl, dinv, resid,
+                                                                      resid_stride, alpha, mll);
+    GPX_LAUNCH_CHECK();
+    return 0;
+}

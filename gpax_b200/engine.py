@@ -1,0 +1,247 @@
+"""Host-side driver of the C-ABI (``include/gpax_b200.h``) on torch CUDA buffers.
+
+torch is used only as the owner of device memory and streams; every numeric
+operation is a call into ``libgpax_b200.so``.  There is no CPU path: calling
+anything here without a CUDA device raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import math
+
+import numpy as np
+import torch
+
+from . import _cabi
+from ._cabi import KernelParams, check, lib
+
+F64 = torch.float64
+
+
+def _require_cuda(dev=None):
+    if not torch.cuda.is_available():
+        raise RuntimeError("gpax_b200 needs a CUDA device (sm_100a); there is no CPU fallback")
+    return torch.device("cuda", torch.cuda.current_device()) if dev is None else torch.device(dev)
+
+
+def _ptr(t):
+    return None if t is None else C.c_void_p(t.data_ptr())
+
+
+def _stream():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _dev(a, dev, dtype=F64):
+    """numpy / tensor -> contiguous device tensor."""
+    if a is None:
+        return None
+    if isinstance(a, torch.Tensor):
+        return a.to(device=dev, dtype=dtype).contiguous()
+    return torch.as_tensor(np.ascontiguousarray(a), dtype=dtype, device=dev)
+
+
+def even(n):
+    return n + (n & 1)
+
+
+class HyperParams:
+    """Device copy of the per-sample hyper-parameter arrays plus the
+    ``gpx_kernel_params`` struct that points at them."""
+
+    def __init__(self, kind, d, hp, dev):
+        self.kind = _cabi.KIND_BY_NAME[kind] if isinstance(kind, str) else int(kind)
+        self.d = int(d)
+        scale = np.atleast_1d(np.asarray(hp["k_scale"], float)).reshape(-1)
+        self.S = scale.shape[0]
+        length = np.asarray(hp["k_length"], float).reshape(self.S, -1)
+        self.dl = length.shape[1]
+        if self.dl not in (1, self.d):
+            raise ValueError(f"k_length must have 1 or d={self.d} columns, got {self.dl}")
+        period = hp.get("k_period")
+        if self.kind == _cabi.PERIODIC:
+            if period is None:
+                raise ValueError("PeriodicKernel needs k_period")
+            period = np.asarray(period, float).reshape(self.S, -1)
+            self.dp = period.shape[1]
+            if self.dp not in (1, self.d):
+                raise ValueError(f"k_period must have 1 or d={self.d} columns, got {self.dp}")
+        else:
+            period, self.dp = None, 0
+        noise = hp.get("k_noise")
+        noise = np.zeros(self.S) if noise is None else np.asarray(noise, float).reshape(-1)
+        jitter = hp.get("k_jitter")
+        jitter = np.full(self.S, 1e-6) if jitter is None else np.asarray(jitter, float).reshape(-1)
+        noise = np.broadcast_to(noise, (self.S,)) if noise.size == 1 else noise
+        jitter = np.broadcast_to(jitter, (self.S,)) if jitter.size == 1 else jitter
+        self.scale = _dev(scale, dev)
+        self.length = _dev(length, dev)
+        self.period = _dev(period, dev)
+        self.noise = _dev(noise, dev)
+        self.jitter = _dev(jitter, dev)
+        self.kp = KernelParams(self.kind, self.d, self.dl, self.dp,
+                               self.scale.data_ptr(), self.length.data_ptr(),
+                               0 if self.period is None else self.period.data_ptr())
+
+
+# ---------------------------------------------------------------------------
+# 1:1 wrappers
+# ---------------------------------------------------------------------------
+def gram(hpd: HyperParams, x1, x2, add_diag=False, noise=None, noise_is_vector=False,
+         noise_sample_stride=0, region=_cabi.FULL, out=None):
+    """``gpx_gram``: returns ``[S, n, ldo]`` (view ``[..., :m]`` is the matrix)."""
+    dev = x1.device
+    n, m = x1.shape[0], x2.shape[0]
+    ldo = even(m)
+    if out is None:
+        out = torch.empty((hpd.S, n, ldo), dtype=F64, device=dev)
+    nz = hpd.noise if noise is None else noise
+    check(lib.gpx_gram(C.byref(hpd.kp), hpd.S, n, m, _ptr(x1), _ptr(x2), _ptr(nz),
+                       1 if noise_is_vector else 0, noise_sample_stride, _ptr(hpd.jitter),
+                       1 if add_diag else 0, region, _ptr(out), ldo, _stream()), "gpx_gram")
+    return out
+
+
+def dinv_alloc(S, n, dev):
+    nbytes = lib.gpx_dinv_bytes(S, n)
+    return torch.empty(nbytes // 8, dtype=F64, device=dev)
+
+
+def potrf(A, n, dinv=None, info=None):
+    S, _, lda = A.shape
+    dev = A.device
+    if dinv is None:
+        dinv = dinv_alloc(S, n, dev)
+    if info is None:
+        info = torch.zeros(S, dtype=torch.int32, device=dev)
+    check(lib.gpx_potrf_batched(S, n, _ptr(A), lda, _ptr(dinv), _ptr(info), _stream()),
+          "gpx_potrf_batched")
+    return dinv, info
+
+
+def trtri(L, n, dinv, W=None):
+    S, _, ldl = L.shape
+    if W is None:
+        W = torch.empty_like(L)
+    check(lib.gpx_trtri_batched(S, n, _ptr(L), ldl, _ptr(dinv), _ptr(W), W.shape[2], _stream()),
+          "gpx_trtri_batched")
+    return W
+
+
+def mll(L, n, dinv, resid, want_alpha=True):
+    """resid: [n] (shared) or [S, n]."""
+    S, _, ldl = L.shape
+    dev = L.device
+    stride = 0 if resid.dim() == 1 else n
+    alpha = torch.empty((S, n), dtype=F64, device=dev) if want_alpha else None
+    val = torch.empty(S, dtype=F64, device=dev)
+    check(lib.gpx_mll(S, n, _ptr(L), ldl, _ptr(dinv), _ptr(resid), stride, _ptr(alpha),
+                      _ptr(val), _stream()), "gpx_mll")
+    return val, alpha
+
+
+def mll_grad(hpd: HyperParams, x, W, alpha):
+    S, n, ldw = W.shape[0], x.shape[0], W.shape[2]
+    dev = W.device
+    ws = torch.empty(max(1, lib.gpx_mll_grad_ws_bytes(S, n, hpd.d) // 8), dtype=F64, device=dev)
+    out = {
+        "k_scale": torch.empty(S, dtype=F64, device=dev),
+        "k_length": torch.empty((S, hpd.dl), dtype=F64, device=dev),
+        "k_noise": torch.empty(S, dtype=F64, device=dev),
+    }
+    dper = None
+    if hpd.dp:
+        dper = out["k_period"] = torch.empty((S, hpd.dp), dtype=F64, device=dev)
+    check(lib.gpx_mll_grad(C.byref(hpd.kp), S, n, _ptr(x), _ptr(W), ldw, _ptr(alpha),
+                           _ptr(out["k_scale"]), _ptr(out["k_length"]), _ptr(dper),
+                           _ptr(out["k_noise"]), _ptr(ws), _stream()), "gpx_mll_grad")
+    return out
+
+
+def predict(hpd: HyperParams, x, x_new, W, alpha, diag_add, m_new=None, m_const=1.0,
+            want_mu=True, want_var=True, mu=None, var=None):
+    S, n, M = hpd.S, x.shape[0], x_new.shape[0]
+    dev = x.device
+    if want_mu and mu is None:
+        mu = torch.empty((S, M), dtype=F64, device=dev)
+    if want_var and var is None:
+        var = torch.empty((S, M), dtype=F64, device=dev)
+    check(lib.gpx_predict(C.byref(hpd.kp), S, n, M, _ptr(x), _ptr(x_new), _ptr(W), W.shape[2],
+                          _ptr(alpha), _ptr(m_new), float(m_const), _ptr(diag_add), _ptr(mu),
+                          _ptr(var), _stream()), "gpx_predict")
+    return mu, var
+
+
+def acq_reduce(mu, var, acq, beta=10.0, y_max=0.0, mu_scale=1.0, mu_shift=0.0, sd_scale=1.0,
+               m_offset=0, want_arrays=True):
+    S, M = mu.shape
+    dev = mu.device
+    P = lib.gpx_acq_parts(M)
+    o_mu = torch.empty(M, dtype=F64, device=dev) if want_arrays else None
+    o_sd = torch.empty(M, dtype=F64, device=dev) if want_arrays else None
+    o_acq = torch.empty(M, dtype=F64, device=dev) if want_arrays else None
+    pv = torch.empty(P, dtype=F64, device=dev)
+    pi = torch.empty(P, dtype=torch.int64, device=dev)
+    check(lib.gpx_acq_reduce(S, M, _ptr(mu), _ptr(var), int(acq), float(beta), float(y_max),
+                             float(mu_scale), float(mu_shift), float(sd_scale), int(m_offset),
+                             _ptr(o_mu), _ptr(o_sd), _ptr(o_acq), _ptr(pv), _ptr(pi), _stream()),
+          "gpx_acq_reduce")
+    return o_mu, o_sd, o_acq, pv, pi
+
+
+def argmax_finalize(pv, pi):
+    dev = pv.device
+    bv = torch.empty(1, dtype=F64, device=dev)
+    bi = torch.empty(1, dtype=torch.int64, device=dev)
+    check(lib.gpx_argmax_finalize(pv.numel(), _ptr(pv), _ptr(pi), _ptr(bv), _ptr(bi), _stream()),
+          "gpx_argmax_finalize")
+    return bv, bi
+
+
+# ---------------------------------------------------------------------------
+# Conditioned posterior state for S hyper-parameter samples
+# ---------------------------------------------------------------------------
+class Posterior:
+    """Device-resident factorisation of ``K_theta_s`` for all samples:
+    Gram (lower) -> Cholesky -> alpha / MLL -> W = L^-1.  Mirrors what
+    ``_get_mean_and_covariance`` (gpax/gp.py:289-300) recomputes on every call,
+    but keeps it cached across predictions."""
+
+    def __init__(self, kind, x, y, hp, m_train=None, y_std=None, device=None, need_w=True):
+        dev = _require_cuda(device)
+        self.dev = dev
+        self.x = _dev(np.asarray(x, float).reshape(len(x), -1), dev)
+        self.n, self.d = self.x.shape
+        self.hpd = HyperParams(kind, self.d, hp, dev)
+        self.S = self.hpd.S
+        y = np.asarray(y, float).reshape(-1)
+        if m_train is None:                      # ConstantMean default 1.0 (gpax/means.py:75-78)
+            resid = y - 1.0
+        else:
+            resid = y[None, :] - np.asarray(m_train, float).reshape(-1, self.n)
+            if resid.shape[0] == 1:
+                resid = resid[0]
+        self.resid = _dev(resid, dev)
+        noise, vec = None, False
+        if y_std is not None:                    # gpax/gp.py:289-290: noise = y_std**2
+            ys = np.broadcast_to(np.atleast_1d(np.asarray(y_std, float)).reshape(-1), (self.n,))
+            noise, vec = _dev(ys**2, dev), True
+        self.L = gram(self.hpd, self.x, self.x, add_diag=True, noise=noise, noise_is_vector=vec,
+                      noise_sample_stride=0, region=_cabi.LOWER)
+        self.dinv, self.info = potrf(self.L, self.n)
+        self.mll, self.alpha = mll(self.L, self.n, self.dinv, self.resid)
+        self.W = trtri(self.L, self.n, self.dinv) if need_w else None
+
+    def predict(self, x_new, m_new=None, m_const=1.0, observation_noise=False,
+                want_mu=True, want_var=True):
+        xn = _dev(np.asarray(x_new, float).reshape(len(x_new), -1), self.dev) \
+            if not isinstance(x_new, torch.Tensor) else x_new
+        diag_add = (self.hpd.noise + self.hpd.jitter) if observation_noise else self.hpd.jitter
+        mn = _dev(m_new, self.dev) if m_new is not None else None
+        return predict(self.hpd, self.x, xn, self.W, self.alpha, diag_add.contiguous(), mn,
+                       m_const, want_mu, want_var)
+
+    def grad(self):
+        g = mll_grad(self.hpd, self.x, self.W, self.alpha)
+        g["resid"] = -self.alpha
+        return g

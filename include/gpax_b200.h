@@ -1,0 +1,176 @@
+/*
+ * gpax_b200.h -- C ABI of the B200-native (sm_100a) exact-GP hot path.
+ *
+ * The reference (matthewcarbone/gpax) has no FFI/plugin interface: its boundary
+ * is the Python call surface, whose numeric bodies are JAX/LAPACK library calls.
+ * Each entry point below replaces one such call site (cited as gpax/<file>:<line>)
+ * and is what a `jax.ffi` custom call / ctypes binding for that site would bind
+ * (see INTEGRATION.md).
+ *
+ * Conventions
+ *  - Every data pointer is a DEVICE pointer to fp64 (double), row-major,
+ *    16-byte aligned; `info` is int32; argmax indices are int64.
+ *  - Batched square matrices are [S, n, ld] with an even leading dimension
+ *    ld >= n (rows start 16-byte aligned).  Only the LOWER triangle (j <= i)
+ *    of a symmetric / triangular matrix is referenced unless stated otherwise.
+ *  - Functions only ENQUEUE work on `stream` (a cudaStream_t passed as void*);
+ *    they never synchronise, never allocate, never touch the host copy of data.
+ *    The caller owns every buffer including workspace (sizes from the *_bytes
+ *    query functions).  All calls are CUDA-graph capturable and re-entrant.
+ *  - Return value: 0 = ok; < 0 = argument #(-rc) invalid; > 0 = cudaError_t.
+ *    Numerical failure (non-SPD pivot) is reported per matrix in `info[S]`
+ *    like LAPACK (0 = ok, k = leading minor of order k not positive).
+ *  - There is no CPU fallback anywhere behind this interface.
+ *
+ * Hyper-parameter arrays (one row per posterior sample s, gpax/gp.py:536-544):
+ *    scale[S]; length[S, dl] (dl = 1 or d, ARD); period[S, dp] (dp = 1 or d;
+ *    PERIODIC only, else NULL/0); noise[S*noise_stride...] see gpx_gram;
+ *    jitter[S].
+ */
+#ifndef GPAX_B200_H
+#define GPAX_B200_H
+
+#include <stdint.h>
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GPX_ABI_VERSION 1
+
+/* covariance families: gpax/kernels.py:110 (RBF), :129 (Matern nu=5/2), :150 (Periodic) */
+enum { GPX_RBF = 0, GPX_MATERN52 = 1, GPX_PERIODIC = 2 };
+/* acquisition: gpax/acquisition.py:291 (EI), :260 (UCB; beta=inf -> UE, beta=0 -> MEAN) */
+enum { GPX_ACQ_EI = 0, GPX_ACQ_UCB = 1, GPX_ACQ_UE = 2, GPX_ACQ_MEAN = 3 };
+/* gram output region */
+enum { GPX_FULL = 0, GPX_LOWER = 1 };
+/* factorisation block size (diagonal-block inverses are [S, ceil(n/GPX_NB), GPX_NB, GPX_NB]) */
+#define GPX_NB 128
+
+/* Shared description of the covariance function and its per-sample parameters. */
+typedef struct gpx_kernel_params {
+    int32_t kind;          /* GPX_RBF | GPX_MATERN52 | GPX_PERIODIC */
+    int32_t d;             /* input dimension (1..GPX_MAX_D) */
+    int32_t dl;            /* columns of length[]: 1 or d */
+    int32_t dp;            /* columns of period[]: 0, 1 or d */
+    const double *scale;   /* [S]      k_scale  */
+    const double *length;  /* [S, dl]  k_length */
+    const double *period;  /* [S, dp]  k_period (PERIODIC) or NULL */
+} gpx_kernel_params;
+#define GPX_MAX_D 8
+
+int gpx_abi_version(void);
+const char *gpx_last_error_string(void);   /* thread-local diagnostic text */
+
+/* ---------------------------------------------------------------------------
+ * gpx_gram: batched Gram matrix  out[s] = k(x1, x2; theta_s)  (+ diag term)
+ * replaces Kernel.__call__/_kernel_function  gpax/kernels.py:93-94,112-168 and
+ * _squared_distance gpax/kernels.py:39-51 (same operation order: scale by 1/l,
+ * norms, X2 - 2XZ + Z2, clip 0).
+ *   x1 [n,d], x2 [m,d]; out [S, n, ldo] (ldo >= m).
+ *   add_diag != 0 and n == m: out[s][i][i] += noise_i + jitter[s]
+ *     (gpax/kernels.py:124-125; the caller evaluates the reference's shape test
+ *     "X1.shape == X2.shape and apply_noise").
+ *   noise: NULL (0.0) | [S] (noise_stride = 0 -> noise[s]) | [S, n] / [n]
+ *     (noise_stride = 1 -> noise[s*noise_sample_stride + i], e.g. y_std**2,
+ *     gpax/gp.py:289-293 with noise_sample_stride = 0).
+ *   region: GPX_FULL, or GPX_LOWER (n == m; only tiles touching j <= i written).
+ */
+int gpx_gram(const gpx_kernel_params *kp, int64_t S, int64_t n, int64_t m,
+             const double *x1, const double *x2,
+             const double *noise, int64_t noise_stride, int64_t noise_sample_stride,
+             const double *jitter, int32_t add_diag, int32_t region,
+             double *out, int64_t ldo, void *stream);
+
+/* ---------------------------------------------------------------------------
+ * gpx_potrf_batched: in-place lower Cholesky  A[s] = L L^T  of S matrices.
+ * replaces jax.scipy.linalg.cho_factor (gpax/gp.py:296) and the
+ * jnp.linalg.cholesky inside numpyro's MultivariateNormal (gpax/gp.py:147-151).
+ *   A [S, n, lda] in: lower triangle of K; out: L (strict upper part of each
+ *   diagonal block is zeroed, other upper blocks untouched).
+ *   dinv [S, ceil(n/GPX_NB), GPX_NB, GPX_NB] out: inverses of the diagonal
+ *   blocks of L (used by the solves below).  info[S].
+ */
+size_t gpx_dinv_bytes(int64_t S, int64_t n);
+int gpx_potrf_batched(int64_t S, int64_t n, double *A, int64_t lda,
+                      double *dinv, int32_t *info, void *stream);
+
+/* gpx_trtri_batched: W[s] = L[s]^-1 (lower), out of place.  No single
+ * reference call site: it is the B200 formulation of the cho_solve of
+ * gpax/gp.py:297 (V = L^-1 K*^T becomes a tensor-core GEMM with W). */
+int gpx_trtri_batched(int64_t S, int64_t n, const double *L, int64_t ldl,
+                      const double *dinv, double *W, int64_t ldw, void *stream);
+
+/* ---------------------------------------------------------------------------
+ * gpx_mll: z = L^-1 resid, alpha = L^-T z, and the numpyro
+ * MultivariateNormal.log_prob value  -0.5 z.z - sum(log L_ii) - n/2 log(2 pi)
+ * replaces gpax/gp.py:147-151 (log density) and cho_solve(K, y - m) gpax/gp.py:300.
+ *   resid [.., n] with sample stride resid_stride (0: shared by all samples).
+ *   alpha [S, n] out (nullable); mll [S] out (nullable).
+ */
+int gpx_mll(int64_t S, int64_t n, const double *L, int64_t ldl, const double *dinv,
+            const double *resid, int64_t resid_stride,
+            double *alpha, double *mll, void *stream);
+
+/* gpx_mll_grad: gradient of the log density above w.r.t. the kernel
+ * hyper-parameters, 0.5 tr((alpha alpha^T - K^-1) dK/dtheta), with K^-1 = W^T W
+ * contracted on the fly (never stored).  Replaces the XLA autodiff backward of
+ * gpax/gp.py:133-151 under NUTS/SVI (gpax/gp.py:515-530, 578-591).
+ *   outputs (nullable): dscale[S], dlength[S,dl], dperiod[S,dp], dnoise[S];
+ *   d/dresid = -alpha (already available from gpx_mll).
+ *   ws: gpx_mll_grad_ws_bytes(S, n, kp->d) bytes. */
+size_t gpx_mll_grad_ws_bytes(int64_t S, int64_t n, int32_t d);
+int gpx_mll_grad(const gpx_kernel_params *kp, int64_t S, int64_t n, const double *x,
+                 const double *W, int64_t ldw, const double *alpha,
+                 double *dscale, double *dlength, double *dperiod, double *dnoise,
+                 void *ws, void *stream);
+
+/* ---------------------------------------------------------------------------
+ * gpx_predict: fused posterior predictive, per sample:
+ *   mu[s,j]  = m_new[s,j] + k*(xnew_j)^T alpha_s
+ *   var[s,j] = k(xnew_j,xnew_j) + diag_add[s] - || W_s k*(xnew_j) ||^2
+ * K* tiles are generated on chip and never written to memory.
+ * replaces GaussianProcess._get_mean_and_covariance (Cholesky branch)
+ * gpax/gp.py:277-301 restricted to diag(cov), which is all that
+ * gpax/gp.py:338,484 consume.
+ *   x [n,d], xnew [M,d]; W [S,n,ldw]; alpha [S,n];
+ *   m_new [S,M] or NULL (-> m_const, ConstantMean gpax/means.py:75-78);
+ *   diag_add [S]: (k_noise if observation_noise else 0) + k_jitter (gpax/gp.py:283-287);
+ *   mu, var [S, M] out (either nullable).
+ */
+int gpx_predict(const gpx_kernel_params *kp, int64_t S, int64_t n, int64_t M,
+                const double *x, const double *xnew,
+                const double *W, int64_t ldw, const double *alpha,
+                const double *m_new, double m_const, const double *diag_add,
+                double *mu, double *var, void *stream);
+
+/* ---------------------------------------------------------------------------
+ * gpx_acq_reduce: mixture moments over S (fixed order s = 0..S-1), reverse
+ * output transform, analytic acquisition and per-block first-max argmax.
+ *   mbar = mean_s mu;  vbar = mean_s(var + mu^2) - mbar^2   (RNG-free limit of
+ *   GPSample.mu/sd, gpax/gp.py:76-90; S == 1 is the analytic `fast` path)
+ *   mu_u = mbar*mu_scale + mu_shift ; sd_u = sqrt(vbar)*sd_scale
+ *     (NormalizeTransform reverse, gpax/transforms.py:312-317)
+ *   acq: EI gpax/acquisition.py:291-298 | UCB :260-266 | UE | MEAN.
+ *   out_mu/out_sd/out_acq [M] nullable.  part_val/part_idx
+ *   [gpx_acq_parts(M)] receive one (value, global index = m_offset + j)
+ *   candidate per block; gpx_argmax_finalize reduces any list of such pairs
+ *   (e.g. the all-gathered per-GPU winners) to the single first maximum
+ *   (jnp.argmax semantics, gpax/acquisition.py:214: lowest index wins ties,
+ *   NaN counts as maximal).
+ */
+int64_t gpx_acq_parts(int64_t M);
+int gpx_acq_reduce(int64_t S, int64_t M, const double *mu, const double *var,
+                   int32_t acq, double beta, double y_max,
+                   double mu_scale, double mu_shift, double sd_scale,
+                   int64_t m_offset,
+                   double *out_mu, double *out_sd, double *out_acq,
+                   double *part_val, int64_t *part_idx, void *stream);
+int gpx_argmax_finalize(int64_t P, const double *part_val, const int64_t *part_idx,
+                        double *best_val, int64_t *best_idx, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GPAX_B200_H */
