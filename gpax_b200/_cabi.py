@@ -46,6 +46,7 @@ _kp = C.POINTER(KernelParams)
 SIGNATURES = {
     "gpx_abi_version": (C.c_int, []),
     "gpx_last_error_string": (C.c_char_p, []),
+    "gpx_launch_count": (C.c_uint64, []),
     "gpx_gram": (C.c_int, [_kp, _i64, _i64, _i64, _ptr, _ptr, _ptr, _i64, _i64, _ptr, _i32,
                            _i32, _ptr, _i64, _ptr]),
     "gpx_dinv_bytes": (_sz, [_i64, _i64]),

@@ -186,6 +186,7 @@ extern "C" int gpx_acq_reduce(int64_t S, int64_t M, const double *mu, const doub
     acq_reduce_kernel<<<grid, A_THREADS, 0, (cudaStream_t)stream>>>(
         S, M, mu, var, acq, coef, y_max, mu_scale, mu_shift, sd_scale, m_offset, out_mu, out_sd,
         out_acq, part_val, part_idx);
+    count_launches(1);
     GPX_LAUNCH_CHECK();
     return 0;
 }
@@ -198,6 +199,7 @@ extern "C" int gpx_argmax_finalize(int64_t P, const double *part_val, const int6
     GPX_ARG_CHECK(part_idx != nullptr, 3);
     argmax_finalize_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(P, part_val, part_idx, best_val,
                                                                  best_idx);
+    count_launches(1);
     GPX_LAUNCH_CHECK();
     return 0;
 }

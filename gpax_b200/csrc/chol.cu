@@ -229,15 +229,19 @@ extern "C" int gpx_potrf_batched(int64_t S, int64_t n, double *A, int64_t lda, d
         if (left && p > 0) {
             dim3 g((unsigned)(T - p), (unsigned)S);
             tile_kernel<OP_SYRK_LEFT><<<g, T_THREADS, T_SMEM_BYTES, st>>>(n, p, A, lda, nullptr, 0, dinv);
+            count_launches(1);
         }
         diag_kernel<<<(unsigned)S, 256, DIAG_SMEM, st>>>(n, p, A, lda, dinv, info);
+        count_launches(1);
         if (p + 1 < T) {
             dim3 g((unsigned)(T - p - 1), (unsigned)S);
             tile_kernel<OP_TRSM><<<g, T_THREADS, T_SMEM_BYTES, st>>>(n, p, A, lda, nullptr, 0, dinv);
+            count_launches(1);
             if (!left) {
                 int64_t tr = T - p - 1;
                 dim3 g2((unsigned)(tr * (tr + 1) / 2), (unsigned)S);
                 tile_kernel<OP_SYRK_RIGHT><<<g2, T_THREADS, T_SMEM_BYTES, st>>>(n, p, A, lda, nullptr, 0, dinv);
+                count_launches(1);
             }
         }
     }
@@ -263,11 +267,13 @@ extern "C" int gpx_trtri_batched(int64_t S, int64_t n, const double *L, int64_t 
     {
         dim3 g((unsigned)T, (unsigned)S);
         trtri_diag_copy_kernel<<<g, 256, 0, st>>>(n, dinv, W, ldw);
+        count_launches(1);
     }
     for (int p = 1; p < T; ++p) {
         dim3 g((unsigned)p, (unsigned)S);
         tile_kernel<OP_TRTRI_ACC><<<g, T_THREADS, T_SMEM_BYTES, st>>>(n, p, W, ldw, L, ldl, dinv);
         tile_kernel<OP_TRTRI_FIN><<<g, T_THREADS, T_SMEM_BYTES, st>>>(n, p, W, ldw, L, ldl, dinv);
+        count_launches(2);
     }
     GPX_LAUNCH_CHECK();
     return 0;

@@ -13,6 +13,7 @@ namespace gpx {
 
 // ---- error plumbing -------------------------------------------------------
 void set_error(const char *fmt, ...);
+void count_launches(int n);   // feeds gpx_launch_count()
 #define GPX_ARG_CHECK(cond, argno)                                             \
     do {                                                                       \
         if (!(cond)) {                                                         \

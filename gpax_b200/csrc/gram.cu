@@ -128,6 +128,7 @@ extern "C" int gpx_gram(const gpx_kernel_params *kp, int64_t S, int64_t n, int64
         default: GPX_GRAM_LAUNCH(GPX_PERIODIC); break;
     }
 #undef GPX_GRAM_LAUNCH
+    count_launches(1);
     GPX_LAUNCH_CHECK();
     return 0;
 }

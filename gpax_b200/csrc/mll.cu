@@ -143,6 +143,7 @@ extern "C" int gpx_mll(int64_t S, int64_t n, const double *L, int64_t ldl, const
     }
     mll_kernel<<<(unsigned)S, MTHREADS, smem, (cudaStream_t)stream>>>(n, L, ldl, dinv, resid,
                                                                       resid_stride, alpha, mll);
+    count_launches(1);
     GPX_LAUNCH_CHECK();
     return 0;
 }

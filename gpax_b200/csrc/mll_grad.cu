@@ -196,6 +196,7 @@ extern "C" int gpx_mll_grad(const gpx_kernel_params *kp, int64_t S, int64_t n, c
                                                                  (double *)ws);
     mll_grad_final_kernel<<<(unsigned)S, 32, 0, st>>>(*kp, ntiles, (const double *)ws, dscale,
                                                        dlength, dperiod, dnoise);
+    count_launches(2);
     GPX_LAUNCH_CHECK();
     return 0;
 }

@@ -324,6 +324,7 @@ extern "C" int gpx_predict(const gpx_kernel_params *kp, int64_t S, int64_t n, in
             break;
     }
     if (rc) return rc;
+    count_launches(1);
     GPX_LAUNCH_CHECK();
     return 0;
 }

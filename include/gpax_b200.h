@@ -62,6 +62,7 @@ typedef struct gpx_kernel_params {
 
 int gpx_abi_version(void);
 const char *gpx_last_error_string(void);   /* thread-local diagnostic text */
+uint64_t gpx_launch_count(void);           /* kernels enqueued by this library so far (process-wide) */
 
 /* ---------------------------------------------------------------------------
  * gpx_gram: batched Gram matrix  out[s] = k(x1, x2; theta_s)  (+ diag term)

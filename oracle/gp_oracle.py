@@ -176,6 +176,8 @@ def mll_and_grad(kind, x, y, m_train, k_scale, k_length, k_noise, k_jitter=1e-6,
     closed form is ``0.5 tr((a a^T - K^-1) dK/dtheta)`` with ``a = K^-1 (y-m)``;
     ``d/dresid = -a``.  Returns ``(mll, dict)``."""
     n = x.shape[0]
+    if isinstance(kind, str):
+        kind = KIND_NAMES[kind]
     K0, dKs, dKl, dKp = _dK_dparams(kind, x, k_scale, k_length, k_period)
     K = K0 + (np.asarray(k_noise) + k_jitter) * np.eye(n)
     resid = y - m_train
@@ -281,6 +283,8 @@ def mixture_moments(mu, var):
     Sequential (s = 0..S-1) accumulation so the device kernel can match the
     summation order bit-for-bit."""
     S = mu.shape[0]
+    if S == 1:          # analytic single-sample path (gpax/gp.py:78-79,86-87)
+        return mu[0].copy(), var[0].copy()
     a = np.zeros(mu.shape[1])
     b = np.zeros(mu.shape[1])
     for s in range(S):
