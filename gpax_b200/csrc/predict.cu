@@ -29,20 +29,28 @@ struct PCfg {
     static constexpr int R = WM * 64;        // W rows per pass
     static constexpr int MT = WN * 32;       // candidates per CTA
     static constexpr int LDW = BK + 4;
-    static constexpr int LDK = BK + 4;
-    static constexpr int EPT = MT * BK / P_THREADS;   // generated elements per thread per slice
+    static constexpr int LDK = WN * 32 + 4;     // K*^T slice stored k-major: [BK][MT+4]
     static constexpr int W_STAGE = R * LDW;
-    static constexpr int KC_ELEMS = MT * LDK;
+    static constexpr int KC_ELEMS = BK * LDK;
     static constexpr size_t SMEM_DOUBLES = (size_t)P_STAGES * W_STAGE + 2 * KC_ELEMS +
                                            3 * BK * P_SX + MT * (GPX_MAX_D + 1) + MT /*colsum*/ +
-                                           WM * MT /*wpart*/ + MT /*mean*/ + 2 * GPX_MAX_D;
+                                           WM * MT /*wpart*/ + P_THREADS /*mean*/ + 2 * GPX_MAX_D;
     static_assert(WM * WN == 8, "8 warps");
-    static_assert(EPT >= 1, "slice too small");
 };
+
+// predicated DMMA: issued only when `on` (warp-uniform) is non-zero, without a
+// branch (no convergence barrier around the tensor instruction)
+__device__ __forceinline__ void dmma884_if(double &c0, double &c1, double a, double b, int on) {
+    asm volatile(
+        "{\n .reg .pred q;\n setp.ne.s32 q, %4, 0;\n"
+        " @q mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n}\n"
+        : "+d"(c0), "+d"(c1)
+        : "d"(a), "d"(b), "r"(on));
+}
 
 template <int KIND, int WM, int WN, int BK>
 __global__ void __launch_bounds__(P_THREADS, 1)
-predict_kernel(gpx_kernel_params kp, int64_t n, int64_t M, const double *__restrict__ x,
+predict_kernel(gpx_kernel_params kp, int n, int M, const double *__restrict__ x,
                const double *__restrict__ xnew, const double *__restrict__ W, int64_t ldw,
                const double *__restrict__ alpha, const double *__restrict__ m_new, double m_const,
                const double *__restrict__ diag_add, double *__restrict__ mu,
@@ -50,17 +58,17 @@ predict_kernel(gpx_kernel_params kp, int64_t n, int64_t M, const double *__restr
     using C = PCfg<WM, WN, BK>;
     extern __shared__ __align__(16) double sm[];
     double *sW = sm;
-    double *sK = sW + P_STAGES * C::W_STAGE;
+    double *sK = sW + P_STAGES * C::W_STAGE;         // [2][BK][LDK]  (k-major)
     double *sX = sK + 2 * C::KC_ELEMS;               // [3][BK][P_SX]
     double *sZ = sX + 3 * BK * P_SX;                 // [MT][MAX_D+1]
     double *colsum = sZ + C::MT * (GPX_MAX_D + 1);   // [MT]
     double *wpart = colsum + C::MT;                  // [WM][MT]
-    double *smean = wpart + WM * C::MT;              // [MT]
-    double *s_len = smean + C::MT;                   // [MAX_D]
+    double *smean = wpart + WM * C::MT;              // [P_THREADS]
+    double *s_len = smean + P_THREADS;               // [MAX_D]
     double *s_per = s_len + GPX_MAX_D;               // [MAX_D]
 
     const int64_t s = blockIdx.y;
-    const int64_t j0 = (int64_t)blockIdx.x * C::MT;
+    const int j0 = blockIdx.x * C::MT;
     const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
     const int wm = warp / WN, wn = warp % WN;
     const int lr = lane >> 2, lc = lane & 3;
@@ -77,10 +85,10 @@ predict_kernel(gpx_kernel_params kp, int64_t n, int64_t M, const double *__restr
     __syncthreads();
     // candidate tile, scaled like the reference scales X1 of k_cross (gpax/gp.py:282)
     for (int e = t; e < C::MT; e += P_THREADS) {
-        const int64_t gj = j0 + e;
+        const int gj = j0 + e;
         double nrm = 0.0;
         for (int q = 0; q < d; ++q) {
-            double v = gj < M ? xnew[gj * d + q] : 0.0;
+            double v = gj < M ? xnew[(size_t)gj * d + q] : 0.0;
             if (KIND != GPX_PERIODIC) v = v / s_len[q];
             sZ[e * (GPX_MAX_D + 1) + q] = v;
             nrm += v * v;
@@ -89,13 +97,13 @@ predict_kernel(gpx_kernel_params kp, int64_t n, int64_t M, const double *__restr
     }
 
     // stage the scaled train points (+ norm, alpha) of slice c into ring slot c % 3
-    auto stage_x = [&](int64_t c) {
+    auto stage_x = [&](int c) {
         if (t < BK) {
-            const int64_t gk = c * BK + t;
+            const int gk = c * BK + t;
             double *dst = sX + ((c % 3) * BK + t) * P_SX;
             double nrm = 0.0;
             for (int q = 0; q < d; ++q) {
-                double v = gk < n ? x[gk * d + q] : 0.0;
+                double v = gk < n ? x[(size_t)gk * d + q] : 0.0;
                 if (KIND != GPX_PERIODIC) v = v / s_len[q];
                 dst[q] = v;
                 nrm += v * v;
@@ -104,39 +112,41 @@ predict_kernel(gpx_kernel_params kp, int64_t n, int64_t M, const double *__restr
             dst[GPX_MAX_D + 1] = gk < n ? al[gk] : 0.0;
         }
     };
-    // issue cp.async for the W slab of slice c (rows rb*R.., cols c*BK..)
-    auto load_w = [&](int64_t rb, int64_t c) {
-        double *dst = sW + (c % P_STAGES) * C::W_STAGE;
-        constexpr int CH_PER_ROW = BK / 2;
-        constexpr int PER_THREAD = C::R * CH_PER_ROW / P_THREADS;
+
+    // ---- W slab loader: thread-constant column pair, rows t/CH + i*ROWS_PER_PASS ----
+    constexpr int CH = BK / 2;                       // 16-byte chunks per row per slice
+    constexpr int ROWS_PER_PASS = P_THREADS / CH;
+    constexpr int PER_THREAD = C::R / ROWS_PER_PASS;
+    const int w_row0 = t / CH, w_kc = (t % CH) * 2;
+    double *const w_dst0 = sW + w_row0 * C::LDW + w_kc;
+    const int64_t w_rowstep = (int64_t)ROWS_PER_PASS * ldw;
+    const double *w_src0 = nullptr;                  // set per row block
+    int w_ivalid = 0;
+    auto load_w = [&](int c) {
+        double *dst = w_dst0 + (c % P_STAGES) * C::W_STAGE;
+        const double *src = w_src0 + c * BK;
+        const int krem = n - (c * BK + w_kc);
+        const int kbytes = krem >= 2 ? 16 : (krem == 1 ? 8 : 0);
 #pragma unroll
         for (int i = 0; i < PER_THREAD; ++i) {
-            int cidx = t + i * P_THREADS;
-            int row = cidx / CH_PER_ROW, kc = (cidx % CH_PER_ROW) * 2;
-            int64_t gr = rb * C::R + row, gk = c * BK + kc;
-            int64_t lim = n - gk;
-            int nbytes = (gr < n) ? (lim >= 2 ? 16 : (lim == 1 ? 8 : 0)) : 0;
-            const double *src = nbytes ? (Ws + gr * ldw + gk) : Ws;
-            cp_async16(dst + row * C::LDW + kc, src, nbytes);
+            const int nbytes = (i < w_ivalid) ? kbytes : 0;
+            cp_async16(dst + i * ROWS_PER_PASS * C::LDW, nbytes ? (src + i * w_rowstep) : Ws, nbytes);
         }
     };
 
-    double macc[C::EPT];
+    // ---- K*^T slice generator: thread-constant candidate j, rows k0 + i*KSTEP ----
+    constexpr int KSTEP = P_THREADS / C::MT > 0 ? P_THREADS / C::MT : 1;
+    constexpr int GEN = (BK + KSTEP - 1) / KSTEP;    // elements per thread per slice
+    const int g_j = t % C::MT, g_k0 = t / C::MT;
+    const double *pz = sZ + g_j * (GPX_MAX_D + 1);
+    double macc = 0.0;
+    auto gen_slice = [&](int c, bool do_mean) {
+        double *dst = sK + (c % 2) * C::KC_ELEMS + g_j;
 #pragma unroll
-    for (int i = 0; i < C::EPT; ++i) macc[i] = 0.0;
-    const int gk_local = t % BK;           // this thread's k inside a slice
-    const int gj_base = t / BK;            // first candidate it generates
-    constexpr int GJ_STEP = P_THREADS / BK;
-
-    // generate slice c of K*^T into sK[c % 2] as [candidate][k]
-    auto gen_slice = [&](int64_t c, bool do_mean) {
-        double *dst = sK + (c % 2) * C::KC_ELEMS;
-        const double *px = sX + ((c % 3) * BK + gk_local) * P_SX;
-        const bool valid = (c * BK + gk_local) < n;
-#pragma unroll
-        for (int i = 0; i < C::EPT; ++i) {
-            const int j = gj_base + i * GJ_STEP;
-            const double *pz = sZ + j * (GPX_MAX_D + 1);
+        for (int i = 0; i < GEN; ++i) {
+            const int kk = g_k0 + i * KSTEP;
+            if (KSTEP * GEN != BK && kk >= BK) break;
+            const double *px = sX + ((c % 3) * BK + kk) * P_SX;
             double v;
             if (KIND == GPX_PERIODIC) {
                 v = k_periodic(pz, px, s_per, s_len, d, scale);
@@ -144,16 +154,18 @@ predict_kernel(gpx_kernel_params kp, int64_t n, int64_t M, const double *__restr
                 double r2 = r2_expansion(pz, pz[GPX_MAX_D], px, px[GPX_MAX_D], d);
                 v = k_from_r2<KIND>(r2, scale);
             }
-            v = valid ? v : 0.0;
-            dst[j * C::LDK + gk_local] = v;
-            if (do_mean) macc[i] = fma(v, px[GPX_MAX_D + 1], macc[i]);
+            v = (c * BK + kk < n) ? v : 0.0;
+            dst[kk * C::LDK] = v;
+            if (do_mean) macc = fma(v, px[GPX_MAX_D + 1], macc);
         }
     };
 
-    const int64_t NRB = (n + C::R - 1) / C::R;
-    for (int64_t rb = 0; rb < NRB; ++rb) {
-        const int64_t kend = (n < (rb + 1) * C::R) ? n : (rb + 1) * C::R;
-        const int64_t nsl = (kend + BK - 1) / BK;
+    const int NRB = (n + C::R - 1) / C::R;
+    for (int rb = 0; rb < NRB; ++rb) {
+        const int kd0 = rb * C::R;                                   // first k of the diagonal block
+        const int kend = (n < kd0 + C::R) ? n : kd0 + C::R;
+        const int nsl = (kend + BK - 1) / BK;
+        const int nsl_full = kd0 / BK;                               // slices strictly below the diagonal
         const bool do_mean = (rb == NRB - 1);
         double acc[P_MF][P_NF][2];
 #pragma unroll
@@ -161,46 +173,67 @@ predict_kernel(gpx_kernel_params kp, int64_t n, int64_t M, const double *__restr
 #pragma unroll
             for (int ni = 0; ni < P_NF; ++ni) acc[mi][ni][0] = acc[mi][ni][1] = 0.0;
 
+        {
+            const int row = kd0 + w_row0;
+            w_src0 = Ws + (int64_t)row * ldw + w_kc;
+            const int rem = n - row;                                  // rows row + i*ROWS_PER_PASS < n
+            w_ivalid = rem <= 0 ? 0 : (rem + ROWS_PER_PASS - 1) / ROWS_PER_PASS;
+        }
         __syncthreads();   // previous row block fully consumed (sK, sX, sW reusable)
         stage_x(0);
         if (nsl > 1) stage_x(1);
 #pragma unroll
         for (int st = 0; st < P_STAGES - 1; ++st) {
-            if (st < nsl) load_w(rb, st);
+            if (st < nsl) load_w(st);
             cp_async_commit();
         }
         __syncthreads();
         gen_slice(0, do_mean);
 
-        for (int64_t c = 0; c < nsl; ++c) {
+        for (int c = 0; c < nsl; ++c) {
             cp_async_wait<P_STAGES - 2>();
             __syncthreads();
-            {
-                int64_t nx = c + P_STAGES - 1;
-                if (nx < nsl) load_w(rb, nx);
-                cp_async_commit();
-            }
+            if (c + P_STAGES - 1 < nsl) load_w(c + P_STAGES - 1);
+            cp_async_commit();
             if (c + 2 < nsl) stage_x(c + 2);
             if (c + 1 < nsl) gen_slice(c + 1, do_mean);
 
-            const double *cW = sW + (c % P_STAGES) * C::W_STAGE;
-            const double *cK = sK + (c % 2) * C::KC_ELEMS;
+            const double *cW = sW + (c % P_STAGES) * C::W_STAGE + lr * C::LDW + lc;
+            const double *cK = sK + (c % 2) * C::KC_ELEMS + lc * C::LDK + wn * 32 + lr;
+            if (c < nsl_full) {
 #pragma unroll
-            for (int ks = 0; ks < BK / 4; ++ks) {
-                const int64_t kg = c * BK + ks * 4;
-                double b[P_NF];
+                for (int ks = 0; ks < BK / 4; ++ks) {
+                    double a[P_MF], b[P_NF];
 #pragma unroll
-                for (int ni = 0; ni < P_NF; ++ni)
-                    b[ni] = cK[(wn * 32 + ni * 8 + lr) * C::LDK + ks * 4 + lc];
+                    for (int ni = 0; ni < P_NF; ++ni) b[ni] = cK[ks * 4 * C::LDK + ni * 8];
 #pragma unroll
-                for (int mi = 0; mi < P_MF; ++mi) {
-                    const int f = wm + WM * mi;                 // cyclic fragment deal
-                    const int64_t rowbase = rb * C::R + f * 8;
-                    if (kg < rowbase + 8 && rowbase < n) {      // below-diagonal k-steps only
-                        double a = cW[(f * 8 + lr) * C::LDW + ks * 4 + lc];
+                    for (int mi = 0; mi < P_MF; ++mi)
+                        a[mi] = cW[((wm + WM * mi) * 8) * C::LDW + ks * 4];
+#pragma unroll
+                    for (int mi = 0; mi < P_MF; ++mi)
 #pragma unroll
                         for (int ni = 0; ni < P_NF; ++ni)
-                            dmma884(acc[mi][ni][0], acc[mi][ni][1], a, b[ni]);
+                            dmma884(acc[mi][ni][0], acc[mi][ni][1], a[mi], b[ni]);
+                }
+            } else {
+                // diagonal block: fragment f = wm + WM*mi needs k_local < 8*(f+1)
+                const int kl = c * BK - kd0;
+#pragma unroll
+                for (int ks = 0; ks < BK / 4; ++ks) {
+                    const int fmin = (kl + ks * 4) >> 3;             // active iff f >= fmin
+                    const int mi0 = (fmin - wm + WM - 1) / WM;       // active iff mi >= mi0
+                    double a[P_MF], b[P_NF];
+#pragma unroll
+                    for (int ni = 0; ni < P_NF; ++ni) b[ni] = cK[ks * 4 * C::LDK + ni * 8];
+#pragma unroll
+                    for (int mi = 0; mi < P_MF; ++mi)
+                        a[mi] = cW[((wm + WM * mi) * 8) * C::LDW + ks * 4];
+#pragma unroll
+                    for (int mi = 0; mi < P_MF; ++mi) {
+                        const int on = (mi >= mi0) ? 1 : 0;
+#pragma unroll
+                        for (int ni = 0; ni < P_NF; ++ni)
+                            dmma884_if(acc[mi][ni][0], acc[mi][ni][1], a[mi], b[ni], on);
                     }
                 }
             }
@@ -234,23 +267,19 @@ predict_kernel(gpx_kernel_params kp, int64_t n, int64_t M, const double *__restr
         }
     }
 
-    // mean: reduce the BK threads that share a candidate (consecutive lanes)
-#pragma unroll
-    for (int i = 0; i < C::EPT; ++i) {
-        double v = macc[i];
-#pragma unroll
-        for (int o = 1; o < BK; o <<= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-        if (gk_local == 0) smean[gj_base + i * GJ_STEP] = v;
-    }
+    // mean: add the partial dot products of the threads that share a candidate
+    smean[t] = macc;
     __syncthreads();
     if (t < C::MT) {
-        const int64_t gj = j0 + t;
+        const int gj = j0 + t;
         if (gj < M) {
             double kd = (KIND == GPX_PERIODIC) ? scale : k_from_r2<KIND == GPX_PERIODIC ? GPX_RBF : KIND>(0.0, scale);
             if (var) var[(size_t)s * M + gj] = (kd + diag_add[s]) - colsum[t];
             if (mu) {
                 double m0 = m_new ? m_new[(size_t)s * M + gj] : m_const;
-                mu[(size_t)s * M + gj] = m0 + smean[t];
+                double dot = 0.0;
+                for (int q = t; q < P_THREADS; q += C::MT) dot += smean[q];
+                mu[(size_t)s * M + gj] = m0 + dot;
             }
         }
     }
@@ -272,7 +301,7 @@ static int launch_predict(const gpx_kernel_params *kp, int64_t S, int64_t n, int
     }
     dim3 grid((unsigned)((M + C::MT - 1) / C::MT), (unsigned)S);
     predict_kernel<KIND, WM, WN, BK><<<grid, P_THREADS, smem, st>>>(
-        *kp, n, M, x, xnew, W, ldw, alpha, m_new, m_const, diag_add, mu, var);
+        *kp, (int)n, (int)M, x, xnew, W, ldw, alpha, m_new, m_const, diag_add, mu, var);
     return 0;
 }
 
@@ -301,8 +330,8 @@ extern "C" int gpx_predict(const gpx_kernel_params *kp, int64_t S, int64_t n, in
     using namespace gpx;
     GPX_ARG_CHECK(validate_kp(kp) == 0, 1);
     GPX_ARG_CHECK(S >= 0 && S <= 65535, 2);
-    GPX_ARG_CHECK(n >= 0, 3);
-    GPX_ARG_CHECK(M >= 0, 4);
+    GPX_ARG_CHECK(n >= 0 && n < (1 << 30), 3);
+    GPX_ARG_CHECK(M >= 0 && M < (1ll << 31) - 512, 4);
     GPX_ARG_CHECK(x != nullptr || n == 0, 5);
     GPX_ARG_CHECK(xnew != nullptr || M == 0, 6);
     GPX_ARG_CHECK(W != nullptr || S * n == 0, 7);
