@@ -247,6 +247,7 @@ def run_ours(args):
     info = torch.zeros(S_local, dtype=torch.int32, device=dev)
     mu = torch.empty((S_local, M), dtype=torch.float64, device=dev)
     var = torch.empty((S_local, M), dtype=torch.float64, device=dev)
+    pws = E.predict_ws_alloc(S_local, n, d, dev)
     ev = {}
 
     def one_step(dev_inputs=None, timed_events=None):
@@ -268,7 +269,7 @@ def run_ours(args):
         E.trtri(bufL, n, dinv, bufW)
         if timed_events is not None:
             timed_events["pred0"].record()
-        E.predict(hpd, di["x"], di["x_new"], bufW, alpha, hpd.jitter, None, 1.0, True, True, mu, var)
+        E.predict(hpd, di["x"], di["x_new"], bufW, alpha, hpd.jitter, None, 1.0, True, True, mu, var, pws)
         if timed_events is not None:
             timed_events["pred1"].record()
         if world > 1:

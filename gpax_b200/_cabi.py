@@ -56,8 +56,9 @@ SIGNATURES = {
     "gpx_mll_grad_ws_bytes": (_sz, [_i64, _i64, _i32]),
     "gpx_mll_grad": (C.c_int, [_kp, _i64, _i64, _ptr, _ptr, _i64, _ptr, _ptr, _ptr, _ptr, _ptr,
                                _ptr, _ptr]),
+    "gpx_predict_ws_bytes": (_sz, [_i64, _i64, _i32]),
     "gpx_predict": (C.c_int, [_kp, _i64, _i64, _i64, _ptr, _ptr, _ptr, _i64, _ptr, _ptr, _dbl,
-                              _ptr, _ptr, _ptr, _ptr]),
+                              _ptr, _ptr, _ptr, _ptr, _ptr]),
     "gpx_acq_parts": (_i64, [_i64]),
     "gpx_acq_reduce": (C.c_int, [_i64, _i64, _ptr, _ptr, _i32, _dbl, _dbl, _dbl, _dbl, _dbl,
                                  _i64, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr]),
@@ -69,7 +70,8 @@ for _name, (_res, _args) in SIGNATURES.items():
     _fn.restype = _res
     _fn.argtypes = _args
 
-if lib.gpx_abi_version() != 1:
+ABI_VERSION = 2
+if lib.gpx_abi_version() != ABI_VERSION:
     raise ImportError("libgpax_b200.so ABI version mismatch")
 
 

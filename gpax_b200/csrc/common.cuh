@@ -50,6 +50,11 @@ __device__ __forceinline__ void cp_async16(void *smem_dst, const void *gsrc, int
                  "r"(src_bytes)
                  : "memory");
 }
+// 8-byte global->shared copy (L1-allocating: the same rows are re-read by many warps)
+__device__ __forceinline__ void cp_async8(void *smem_dst, const void *gsrc) {
+    unsigned s = (unsigned)__cvta_generic_to_shared(smem_dst);
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;\n" ::"r"(s), "l"(gsrc) : "memory");
+}
 __device__ __forceinline__ void cp_async_commit() {
     asm volatile("cp.async.commit_group;\n" ::: "memory");
 }
@@ -72,6 +77,108 @@ __device__ __forceinline__ double k_from_r2(double r2, double scale) {
         double r = sqrt(r2 + 1e-12);
         double s5r = GPX_SQRT5 * r;
         return scale * (1.0 + s5r + GPX_5_3 * r2) * exp(-s5r);
+    }
+}
+
+// ---- branch-free, N-wide fp64 exp / sqrt ------------------------------------
+// The K* generators evaluate N independent covariance entries per thread.  CUDA's
+// exp()/sqrt() carry special-case branches that keep the compiler from
+// interleaving the N dependency chains; on B200 the FP64 ALU shares its pipe
+// with DMMA, so a producer warp gets an issue slot only every few tens of cycles
+// and must have several independent operations ready each time.  These versions
+// are straight-line code written "array style" so the N chains interleave.
+//   exp_vec : Cody-Waite reduction by ln2 (fdlibm split), Taylor degree 13 on
+//             |r| <= ln2/2 (truncation 4e-18 relative), two-step 2^n scaling so
+//             subnormal results round correctly; arguments below -1000 give 0.
+//             Max observed error 1 ulp vs correctly rounded (tests/test_gpu_kernels.py).
+//   sqrt_vec: MUFU rsqrt seed, two Newton steps, FMA residual correction; valid
+//             for normal positive arguments (here r2 + 1e-12 >= 1e-12).
+template <int N>
+__device__ __forceinline__ void exp_vec(double (&x)[N]) {
+    const double L2E = 1.4426950408889634, SHIFT = 6755399441055744.0;   // 1.5 * 2^52
+    const double LN2_HI = 6.93147180369123816490e-01, LN2_LO = 1.90821492927058770002e-10;
+    int ni[N];
+    double nf[N], p[N];
+#pragma unroll
+    for (int i = 0; i < N; ++i) x[i] = fmax(x[i], -1000.0);
+#pragma unroll
+    for (int i = 0; i < N; ++i) {
+        double t = fma(x[i], L2E, SHIFT);
+        ni[i] = __double2loint(t);
+        nf[i] = t - SHIFT;
+    }
+#pragma unroll
+    for (int i = 0; i < N; ++i) x[i] = fma(nf[i], -LN2_HI, x[i]);
+#pragma unroll
+    for (int i = 0; i < N; ++i) x[i] = fma(nf[i], -LN2_LO, x[i]);
+    const double c[14] = {1.0, 1.0, 0.5, 1.6666666666666666e-01, 4.1666666666666664e-02,
+                          8.3333333333333332e-03, 1.3888888888888889e-03, 1.9841269841269841e-04,
+                          2.4801587301587302e-05, 2.7557319223985893e-06, 2.7557319223985888e-07,
+                          2.5052108385441720e-08, 2.0876756987868100e-09, 1.6059043836821613e-10};
+#pragma unroll
+    for (int i = 0; i < N; ++i) p[i] = fma(c[13], x[i], c[12]);
+#pragma unroll
+    for (int k = 11; k >= 0; --k) {
+#pragma unroll
+        for (int i = 0; i < N; ++i) p[i] = fma(p[i], x[i], c[k]);
+    }
+#pragma unroll
+    for (int i = 0; i < N; ++i) {
+        const int n1 = ni[i] >> 1, n2 = ni[i] - n1;
+        p[i] *= __hiloint2double((n1 + 1023) << 20, 0);
+        x[i] = p[i] * __hiloint2double((n2 + 1023) << 20, 0);
+    }
+}
+
+template <int N>
+__device__ __forceinline__ void sqrt_vec(double (&a)[N]) {
+    double y[N], h[N];
+#pragma unroll
+    for (int i = 0; i < N; ++i) {
+        asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y[i]) : "d"(a[i]));
+        h[i] = 0.5 * a[i];
+    }
+#pragma unroll
+    for (int it = 0; it < 2; ++it) {
+#pragma unroll
+        for (int i = 0; i < N; ++i) {
+            double t = y[i] * y[i];
+            double u = fma(-h[i], t, 1.5);
+            y[i] = y[i] * u;
+        }
+    }
+#pragma unroll
+    for (int i = 0; i < N; ++i) {
+        double sq = a[i] * y[i];
+        double e = fma(-sq, sq, a[i]);
+        a[i] = fma(e, 0.5 * y[i], sq);
+    }
+}
+
+// N covariance values from N clipped scaled squared distances (in place),
+// same formulas / association order as k_from_r2
+template <int KIND, int N>
+__device__ __forceinline__ void k_from_r2_vec(double (&v)[N], double scale) {
+    if (KIND == GPX_RBF) {
+#pragma unroll
+        for (int i = 0; i < N; ++i) v[i] = -0.5 * v[i];
+        exp_vec<N>(v);
+#pragma unroll
+        for (int i = 0; i < N; ++i) v[i] = scale * v[i];
+    } else {
+        double r[N], pl[N];
+#pragma unroll
+        for (int i = 0; i < N; ++i) r[i] = v[i] + 1e-12;
+        sqrt_vec<N>(r);
+#pragma unroll
+        for (int i = 0; i < N; ++i) {
+            r[i] = GPX_SQRT5 * r[i];
+            pl[i] = scale * (1.0 + r[i] + GPX_5_3 * v[i]);
+            r[i] = -r[i];
+        }
+        exp_vec<N>(r);
+#pragma unroll
+        for (int i = 0; i < N; ++i) v[i] = pl[i] * r[i];
     }
 }
 

@@ -5,86 +5,168 @@
 //     mu[s,j]  = m_new[s,j] + k*_j . alpha_s
 //     var[s,j] = k(x*_j,x*_j) + diag_add[s] - || W_s k*_j ||^2 ,  W_s = L_s^-1
 //
-// One CTA owns (sample s, tile of MT candidates).  K*^T is generated on chip in
-// BK-row slices (reference operation order: divide by the length scale, norms,
-// X2 - 2XZ + Z2, clip; gpax/kernels.py:39-51) straight into shared memory and is
-// consumed as the B operand of FP64 DMMAs whose A operand, a slab of R rows of
-// W_s, streams from L2/HBM through a cp.async ring.  V = W K*^T is never stored:
-// its column sums of squares are reduced in registers.  The K* tile therefore
-// never touches HBM (north_star item 3).  Row blocks are walked top to bottom
-// and only k-steps below the diagonal of each 8-row fragment are issued
-// (W is lower triangular); fragments are dealt cyclically to the warps so the
-// triangular skipping stays load-balanced.
-#include "common.cuh"
+// Large-n kernel (n > 128): warp-specialised, one CTA per (sample s, tile of MT
+// candidates), 12 warps:
+//   * warps 0-7  CONSUMERS: FP64 DMMA (mma.sync m8n8k4) over a slab of R rows of
+//     W_s times the K*^T slice, accumulators in registers, then the column sums
+//     of squares of V = W K*^T (V is never stored).
+//   * warps 8-11 PRODUCERS: one elected thread streams the W slab of each
+//     16-column slice with TMA (cp.async.bulk.tensor, 128-byte swizzle, the
+//     layout the DMMA A-fragment loads read conflict-free); all 128 threads
+//     generate the K*^T slice on chip (reference operation order: divide by the
+//     length scale, norms, X2 - 2XZ + Z2, clip; gpax/kernels.py:39-51) and
+//     accumulate the mean k*.alpha.  K* never touches HBM (north_star item 3).
+//   Stages are handed over through full/empty mbarriers; registers are moved
+//   from the producer to the consumer warpgroups with setmaxnreg.
+// W is lower triangular: row blocks are walked top to bottom, only k-steps at
+// or below the diagonal of each 8-row fragment are issued (warp-uniform
+// branches), and fragments are dealt cyclically to the warps so the triangular
+// skipping stays load-balanced.
+//
+// The scaled training inputs (x / length, their squared norms) and alpha are
+// staged once per call into a small workspace xs[S][n][d+2] by a prep kernel.
+#include <cuda.h>
+#include "predict_small.cuh"
 
 namespace gpx {
 
-constexpr int P_THREADS = 256;
-constexpr int P_STAGES = 3;
-constexpr int P_MF = 8, P_NF = 4;      // per-warp fragment grid (64 rows x 32 cols)
-constexpr int P_SX = GPX_MAX_D + 2;    // staged train point: d coords, [MAX_D]=norm, [MAX_D+1]=alpha
+constexpr int W_CONS_WARPS = 8;
+constexpr int W_PROD_WARPS = 4;
+constexpr int W_THREADS = (W_CONS_WARPS + W_PROD_WARPS) * 32;   // 384
+constexpr int W_PROD_THREADS = W_PROD_WARPS * 32;               // 128
+constexpr int W_BK = 16;                                        // 128-byte rows = one swizzle span
+constexpr int W_REGS_CONS = 208, W_REGS_PROD = 88;              // 256*208 + 128*88 = 384*168
+constexpr int W_XS = GPX_MAX_D + 2;                             // staged training row: coords, norm, alpha
 
-template <int WM, int WN, int BK>
-struct PCfg {
-    static constexpr int R = WM * 64;        // W rows per pass
-    static constexpr int MT = WN * 32;       // candidates per CTA
-    static constexpr int LDW = BK + 4;
-    static constexpr int LDK = WN * 32 + 4;     // K*^T slice stored k-major: [BK][MT+4]
-    static constexpr int W_STAGE = R * LDW;
-    static constexpr int KC_ELEMS = BK * LDK;
-    static constexpr size_t SMEM_DOUBLES = (size_t)P_STAGES * W_STAGE + 2 * KC_ELEMS +
-                                           3 * BK * P_SX + MT * (GPX_MAX_D + 1) + MT /*colsum*/ +
-                                           WM * MT /*wpart*/ + P_THREADS /*mean*/ + 2 * GPX_MAX_D;
-    static_assert(WM * WN == 8, "8 warps");
+template <int WM, int WN>
+struct WCfg {
+    static_assert(WM * WN == W_CONS_WARPS, "8 consumer warps");
+    static constexpr int R = WM * 64;          // W rows per pass
+    static constexpr int MT = WN * 32;         // candidates per CTA
+    static constexpr int NST = (R >= 512) ? 3 : 4;
+    static constexpr int LDK = MT + 4;         // K*^T slice, k-major [W_BK][LDK]
+    static constexpr int W_STAGE = R * W_BK;   // doubles (R * 128 bytes, multiple of 1024)
+    static constexpr int K_STAGE = W_BK * LDK;
+    static constexpr int BOX_ROWS = (R > 256) ? 256 : R;
+    static constexpr int NBOX = R / BOX_ROWS;
+    static constexpr size_t SMEM_BYTES =
+        1024 /*alignment slack*/ +
+        sizeof(double) * ((size_t)NST * W_STAGE + (size_t)NST * K_STAGE + MT * (GPX_MAX_D + 1) +
+                          MT /*colsum*/ + WM * MT /*wpart*/ + W_PROD_THREADS /*smean*/ +
+                          2 * GPX_MAX_D + W_PROD_WARPS * 2 * W_BK * W_XS /*sXW (upper bound)*/) +
+        sizeof(uint64_t) * 2 * NST;
 };
 
-// predicated DMMA: issued only when `on` (warp-uniform) is non-zero, without a
-// branch (no convergence barrier around the tensor instruction)
-__device__ __forceinline__ void dmma884_if(double &c0, double &c1, double a, double b, int on) {
+// ---- mbarrier / TMA primitives (PTX) ---------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void *p) {
+    return (uint32_t)__cvta_generic_to_shared(p);
+}
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;\n" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];\n" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;\n" ::"r"(bar), "r"(bytes)
+                 : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
     asm volatile(
-        "{\n .reg .pred q;\n setp.ne.s32 q, %4, 0;\n"
-        " @q mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n}\n"
-        : "+d"(c0), "+d"(c1)
-        : "d"(a), "d"(b), "r"(on));
+        "{\n .reg .pred p;\n"
+        "WAIT_LOOP:\n"
+        " mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        " @p bra WAIT_DONE;\n"
+        " bra WAIT_LOOP;\n"
+        "WAIT_DONE:\n}\n" ::"r"(bar), "r"(parity)
+        : "memory");
+}
+__device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap *tm, uint32_t bar,
+                                            int c0, int c1, int c2) {
+    asm volatile(
+        "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes "
+        "[%0], [%1, {%3, %4, %5}], [%2];\n" ::"r"(dst), "l"(tm), "r"(bar), "r"(c0), "r"(c1), "r"(c2)
+        : "memory");
+}
+__device__ __forceinline__ void consumer_bar_sync() {
+    asm volatile("bar.sync 1, %0;\n" ::"n"(W_CONS_WARPS * 32) : "memory");
 }
 
-template <int KIND, int WM, int WN, int BK>
-__global__ void __launch_bounds__(P_THREADS, 1)
-predict_kernel(gpx_kernel_params kp, int n, int M, const double *__restrict__ x,
-               const double *__restrict__ xnew, const double *__restrict__ W, int64_t ldw,
-               const double *__restrict__ alpha, const double *__restrict__ m_new, double m_const,
-               const double *__restrict__ diag_add, double *__restrict__ mu,
-               double *__restrict__ var) {
-    using C = PCfg<WM, WN, BK>;
-    extern __shared__ __align__(16) double sm[];
-    double *sW = sm;
-    double *sK = sW + P_STAGES * C::W_STAGE;         // [2][BK][LDK]  (k-major)
-    double *sX = sK + 2 * C::KC_ELEMS;               // [3][BK][P_SX]
-    double *sZ = sX + 3 * BK * P_SX;                 // [MT][MAX_D+1]
-    double *colsum = sZ + C::MT * (GPX_MAX_D + 1);   // [MT]
-    double *wpart = colsum + C::MT;                  // [WM][MT]
-    double *smean = wpart + WM * C::MT;              // [P_THREADS]
-    double *s_len = smean + P_THREADS;               // [MAX_D]
-    double *s_per = s_len + GPX_MAX_D;               // [MAX_D]
-
+// ---------------------------------------------------------------------------
+// prep: xs[s][k][0..d-1] = x_k / length_s (raw x for PERIODIC), [d] = squared
+// norm of the scaled point, [d+1] = alpha_s[k]
+// ---------------------------------------------------------------------------
+template <int KIND>
+__global__ void __launch_bounds__(256)
+predict_prep_kernel(gpx_kernel_params kp, int n, const double *__restrict__ x,
+                    const double *__restrict__ alpha, double *__restrict__ xs) {
     const int64_t s = blockIdx.y;
+    const int k = blockIdx.x * 256 + threadIdx.x;
+    if (k >= n) return;
+    const int d = kp.d, XS = d + 2;
+    double *dst = xs + ((size_t)s * n + k) * XS;
+    double nrm = 0.0;
+    for (int q = 0; q < d; ++q) {
+        double v = x[(size_t)k * d + q];
+        if (KIND != GPX_PERIODIC) v = v / len_of(kp, s, q);
+        dst[q] = v;
+        nrm += v * v;
+    }
+    dst[d] = nrm;
+    dst[d + 1] = alpha[(size_t)s * n + k];
+}
+
+// ---------------------------------------------------------------------------
+// main kernel
+// ---------------------------------------------------------------------------
+template <int KIND, int WM, int WN>
+__global__ void __launch_bounds__(W_THREADS, 1)
+predict_ws_kernel(const __grid_constant__ CUtensorMap tmW, gpx_kernel_params kp, int n, int M,
+                  const double *__restrict__ xs, const double *__restrict__ xnew,
+                  const double *__restrict__ m_new, double m_const,
+                  const double *__restrict__ diag_add, double *__restrict__ mu,
+                  double *__restrict__ var) {
+    using C = WCfg<WM, WN>;
+    extern __shared__ unsigned char smem_raw[];
+    // 1024-byte alignment: the 128-byte TMA swizzle pattern is a function of the
+    // shared-memory address bits [4:9]
+    double *sW = reinterpret_cast<double *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                            ~(uintptr_t)1023);
+    double *sK = sW + (size_t)C::NST * C::W_STAGE;        // [NST][W_BK][LDK]
+    double *sZ = sK + (size_t)C::NST * C::K_STAGE;        // [MT][MAX_D+1]
+    double *colsum = sZ + C::MT * (GPX_MAX_D + 1);        // [MT]
+    double *wpart = colsum + C::MT;                       // [WM][MT]
+    double *smean = wpart + WM * C::MT;                   // [W_PROD_THREADS]
+    double *s_len = smean + W_PROD_THREADS;               // [MAX_D]
+    double *s_per = s_len + GPX_MAX_D;                    // [MAX_D]
+    double *sXW = s_per + GPX_MAX_D;                      // [W_PROD_WARPS][2][GEN][W_XS]
+    uint64_t *bars = reinterpret_cast<uint64_t *>(sXW + W_PROD_WARPS * 2 * W_BK * W_XS);   // full[NST], empty[NST]
+
+    const int s = blockIdx.y;
     const int j0 = blockIdx.x * C::MT;
     const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
-    const int wm = warp / WN, wn = warp % WN;
-    const int lr = lane >> 2, lc = lane & 3;
     const int d = kp.d;
     const double scale = kp.scale[s];
-    const double *Ws = W + (size_t)s * n * ldw;
-    const double *al = alpha + (size_t)s * n;
+    const uint32_t bar_full = smem_u32(bars), bar_empty = smem_u32(bars + C::NST);
 
     if (t < d) {
         s_len[t] = len_of(kp, s, t);
         s_per[t] = per_of(kp, s, t);
     }
     if (t < C::MT) colsum[t] = 0.0;
+    if (t == 0) {
+#pragma unroll
+        for (int i = 0; i < C::NST; ++i) {
+            mbar_init(bar_full + 8 * i, W_PROD_THREADS + 1);   // producers + the expect_tx arrive
+            mbar_init(bar_empty + 8 * i, W_CONS_WARPS);        // one elected lane per consumer warp
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
+        asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory");
+        asm volatile("prefetch.tensormap [%0];\n" ::"l"(&tmW) : "memory");
+    }
     __syncthreads();
     // candidate tile, scaled like the reference scales X1 of k_cross (gpax/gp.py:282)
-    for (int e = t; e < C::MT; e += P_THREADS) {
+    for (int e = t; e < C::MT; e += W_THREADS) {
         const int gj = j0 + e;
         double nrm = 0.0;
         for (int q = 0; q < d; ++q) {
@@ -95,213 +177,295 @@ predict_kernel(gpx_kernel_params kp, int n, int M, const double *__restrict__ x,
         }
         sZ[e * (GPX_MAX_D + 1) + GPX_MAX_D] = nrm;
     }
-
-    // stage the scaled train points (+ norm, alpha) of slice c into ring slot c % 3
-    auto stage_x = [&](int c) {
-        if (t < BK) {
-            const int gk = c * BK + t;
-            double *dst = sX + ((c % 3) * BK + t) * P_SX;
-            double nrm = 0.0;
-            for (int q = 0; q < d; ++q) {
-                double v = gk < n ? x[(size_t)gk * d + q] : 0.0;
-                if (KIND != GPX_PERIODIC) v = v / s_len[q];
-                dst[q] = v;
-                nrm += v * v;
-            }
-            dst[GPX_MAX_D] = nrm;
-            dst[GPX_MAX_D + 1] = gk < n ? al[gk] : 0.0;
-        }
-    };
-
-    // ---- W slab loader: thread-constant column pair, rows t/CH + i*ROWS_PER_PASS ----
-    constexpr int CH = BK / 2;                       // 16-byte chunks per row per slice
-    constexpr int ROWS_PER_PASS = P_THREADS / CH;
-    constexpr int PER_THREAD = C::R / ROWS_PER_PASS;
-    const int w_row0 = t / CH, w_kc = (t % CH) * 2;
-    double *const w_dst0 = sW + w_row0 * C::LDW + w_kc;
-    const int64_t w_rowstep = (int64_t)ROWS_PER_PASS * ldw;
-    const double *w_src0 = nullptr;                  // set per row block
-    int w_ivalid = 0;
-    auto load_w = [&](int c) {
-        double *dst = w_dst0 + (c % P_STAGES) * C::W_STAGE;
-        const double *src = w_src0 + c * BK;
-        const int krem = n - (c * BK + w_kc);
-        const int kbytes = krem >= 2 ? 16 : (krem == 1 ? 8 : 0);
-#pragma unroll
-        for (int i = 0; i < PER_THREAD; ++i) {
-            const int nbytes = (i < w_ivalid) ? kbytes : 0;
-            cp_async16(dst + i * ROWS_PER_PASS * C::LDW, nbytes ? (src + i * w_rowstep) : Ws, nbytes);
-        }
-    };
-
-    // ---- K*^T slice generator: thread-constant candidate j, rows k0 + i*KSTEP ----
-    constexpr int KSTEP = P_THREADS / C::MT > 0 ? P_THREADS / C::MT : 1;
-    constexpr int GEN = (BK + KSTEP - 1) / KSTEP;    // elements per thread per slice
-    const int g_j = t % C::MT, g_k0 = t / C::MT;
-    const double *pz = sZ + g_j * (GPX_MAX_D + 1);
-    double macc = 0.0;
-    auto gen_slice = [&](int c, bool do_mean) {
-        double *dst = sK + (c % 2) * C::KC_ELEMS + g_j;
-#pragma unroll
-        for (int i = 0; i < GEN; ++i) {
-            const int kk = g_k0 + i * KSTEP;
-            if (KSTEP * GEN != BK && kk >= BK) break;
-            const double *px = sX + ((c % 3) * BK + kk) * P_SX;
-            double v;
-            if (KIND == GPX_PERIODIC) {
-                v = k_periodic(pz, px, s_per, s_len, d, scale);
-            } else {
-                double r2 = r2_expansion(pz, pz[GPX_MAX_D], px, px[GPX_MAX_D], d);
-                v = k_from_r2<KIND>(r2, scale);
-            }
-            v = (c * BK + kk < n) ? v : 0.0;
-            dst[kk * C::LDK] = v;
-            if (do_mean) macc = fma(v, px[GPX_MAX_D + 1], macc);
-        }
-    };
+    __syncthreads();
 
     const int NRB = (n + C::R - 1) / C::R;
-    for (int rb = 0; rb < NRB; ++rb) {
-        const int kd0 = rb * C::R;                                   // first k of the diagonal block
-        const int kend = (n < kd0 + C::R) ? n : kd0 + C::R;
-        const int nsl = (kend + BK - 1) / BK;
-        const int nsl_full = kd0 / BK;                               // slices strictly below the diagonal
-        const bool do_mean = (rb == NRB - 1);
-        double acc[P_MF][P_NF][2];
-#pragma unroll
-        for (int mi = 0; mi < P_MF; ++mi)
-#pragma unroll
-            for (int ni = 0; ni < P_NF; ++ni) acc[mi][ni][0] = acc[mi][ni][1] = 0.0;
 
-        {
-            const int row = kd0 + w_row0;
-            w_src0 = Ws + (int64_t)row * ldw + w_kc;
-            const int rem = n - row;                                  // rows row + i*ROWS_PER_PASS < n
-            w_ivalid = rem <= 0 ? 0 : (rem + ROWS_PER_PASS - 1) / ROWS_PER_PASS;
+    if (warp >= W_CONS_WARPS) {
+        // =========================== PRODUCERS ===========================
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;\n" ::"n"(W_REGS_PROD));
+        const int pt = t - W_CONS_WARPS * 32;                    // 0..127
+        const int pw = pt >> 5;
+        constexpr int KSTEP = W_PROD_THREADS / C::MT;            // k rows generated per pass
+        constexpr int GEN = W_BK / KSTEP;                        // elements per thread per slice
+        static_assert(KSTEP >= 1 && KSTEP * GEN == W_BK, "producer mapping");
+        const int g_j = pt % C::MT, g_k0 = pt / C::MT;           // g_k0 is warp-uniform
+        const double *pz = sZ + g_j * (GPX_MAX_D + 1);
+        const int XS = d + 2;
+        const double *xs_s = xs + (size_t)s * n * XS;
+        const double z2n = pz[GPX_MAX_D];
+        // warp-private double buffer of the GEN staged training rows of a slice
+        // (scaled coordinates, norm, alpha), prefetched one slice ahead with cp.async
+        double *xw = sXW + pw * (2 * GEN * W_XS);
+        int cp_i[3], cp_col[3];
+#pragma unroll
+        for (int e = 0; e < 3; ++e) {
+            const int idx = lane + 32 * e;
+            cp_i[e] = idx < GEN * XS ? idx / XS : -1;
+            cp_col[e] = idx % XS;
         }
-        __syncthreads();   // previous row block fully consumed (sK, sX, sW reusable)
-        stage_x(0);
-        if (nsl > 1) stage_x(1);
+        auto prefetch_rows = [&](int c, int buf) {
 #pragma unroll
-        for (int st = 0; st < P_STAGES - 1; ++st) {
-            if (st < nsl) load_w(st);
-            cp_async_commit();
-        }
-        __syncthreads();
-        gen_slice(0, do_mean);
-
-        for (int c = 0; c < nsl; ++c) {
-            cp_async_wait<P_STAGES - 2>();
-            __syncthreads();
-            if (c + P_STAGES - 1 < nsl) load_w(c + P_STAGES - 1);
-            cp_async_commit();
-            if (c + 2 < nsl) stage_x(c + 2);
-            if (c + 1 < nsl) gen_slice(c + 1, do_mean);
-
-            const double *cW = sW + (c % P_STAGES) * C::W_STAGE + lr * C::LDW + lc;
-            const double *cK = sK + (c % 2) * C::KC_ELEMS + lc * C::LDK + wn * 32 + lr;
-            if (c < nsl_full) {
-#pragma unroll
-                for (int ks = 0; ks < BK / 4; ++ks) {
-                    double a[P_MF], b[P_NF];
-#pragma unroll
-                    for (int ni = 0; ni < P_NF; ++ni) b[ni] = cK[ks * 4 * C::LDK + ni * 8];
-#pragma unroll
-                    for (int mi = 0; mi < P_MF; ++mi)
-                        a[mi] = cW[((wm + WM * mi) * 8) * C::LDW + ks * 4];
-#pragma unroll
-                    for (int mi = 0; mi < P_MF; ++mi)
-#pragma unroll
-                        for (int ni = 0; ni < P_NF; ++ni)
-                            dmma884(acc[mi][ni][0], acc[mi][ni][1], a[mi], b[ni]);
+            for (int e = 0; e < 3; ++e) {
+                if (cp_i[e] >= 0) {
+                    int gk = c * W_BK + g_k0 + cp_i[e] * KSTEP;
+                    gk = gk < n ? gk : n - 1;
+                    cp_async8(xw + (buf * GEN + cp_i[e]) * W_XS + cp_col[e],
+                              xs_s + (size_t)gk * XS + cp_col[e]);
                 }
-            } else {
-                // diagonal block: fragment f = wm + WM*mi needs k_local < 8*(f+1)
-                const int kl = c * BK - kd0;
+            }
+            cp_async_commit();
+        };
+        double macc = 0.0;
+        uint32_t it = 0;
+        prefetch_rows(0, 0);
+        for (int rb = 0; rb < NRB; ++rb) {
+            const int kd0 = rb * C::R;
+            const int kend = (n < kd0 + C::R) ? n : kd0 + C::R;
+            const int nsl = (kend + W_BK - 1) / W_BK;
+            const bool do_mean = (rb == NRB - 1);
+            for (int c = 0; c < nsl; ++c, ++it) {
+                const uint32_t st = it % C::NST, ph = (it / C::NST) & 1;
+                const int buf = it & 1;
+                __syncwarp();                                    // everyone is done with buf ^ 1
+                prefetch_rows((c + 1 < nsl) ? c + 1 : 0, buf ^ 1);   // next slice (or first of next pass)
+                mbar_wait(bar_empty + 8 * st, ph ^ 1);
+                if (pt == 0) {
+                    mbar_arrive_expect_tx(bar_full + 8 * st, (uint32_t)(C::W_STAGE * sizeof(double)));
 #pragma unroll
-                for (int ks = 0; ks < BK / 4; ++ks) {
-                    const int fmin = (kl + ks * 4) >> 3;             // active iff f >= fmin
-                    const int mi0 = (fmin - wm + WM - 1) / WM;       // active iff mi >= mi0
-                    double a[P_MF], b[P_NF];
+                    for (int b = 0; b < C::NBOX; ++b)
+                        tma_load_3d(smem_u32(sW + (size_t)st * C::W_STAGE + b * C::BOX_ROWS * W_BK),
+                                    &tmW, bar_full + 8 * st, c * W_BK, kd0 + b * C::BOX_ROWS, s);
+                }
+                cp_async_wait<1>();
+                __syncwarp();                                    // the warp's rows of slice c landed
+                const double *rows = xw + buf * GEN * W_XS;
+                double *dst = sK + (size_t)st * C::K_STAGE + g_j;
+                double v[GEN], al[GEN];
+                if (KIND == GPX_PERIODIC) {
 #pragma unroll
-                    for (int ni = 0; ni < P_NF; ++ni) b[ni] = cK[ks * 4 * C::LDK + ni * 8];
+                    for (int i = 0; i < GEN; ++i) {
+                        const double *px = rows + i * W_XS;
+                        double acc = 0.0;
+                        for (int q = 0; q < d; ++q) {
+                            double df = pz[q] - px[q];
+                            double sn = sin(GPX_PI * df / s_per[q]) / s_len[q];
+                            acc += sn * sn;
+                        }
+                        v[i] = -2.0 * acc;
+                        al[i] = px[d + 1];
+                    }
 #pragma unroll
-                    for (int mi = 0; mi < P_MF; ++mi)
-                        a[mi] = cW[((wm + WM * mi) * 8) * C::LDW + ks * 4];
+                    for (int i = 0; i < GEN; ++i) v[i] = scale * exp(v[i]);
+                } else {
 #pragma unroll
-                    for (int mi = 0; mi < P_MF; ++mi) {
-                        const int on = (mi >= mi0) ? 1 : 0;
+                    for (int i = 0; i < GEN; ++i) {
+                        const double *px = rows + i * W_XS;
+                        double xz = 0.0;
+                        for (int q = 0; q < d; ++q) xz = fma(pz[q], px[q], xz);
+                        v[i] = fmax((z2n - 2.0 * xz) + px[d], 0.0);
+                        al[i] = px[d + 1];
+                    }
+                    // N-wide straight-line exp/sqrt so the chains interleave (common.cuh)
+                    constexpr int GB = GEN < 4 ? GEN : 4;
 #pragma unroll
-                        for (int ni = 0; ni < P_NF; ++ni)
-                            dmma884_if(acc[mi][ni][0], acc[mi][ni][1], a[mi], b[ni], on);
+                    for (int g = 0; g < GEN / GB; ++g) {
+                        double w[GB];
+#pragma unroll
+                        for (int i = 0; i < GB; ++i) w[i] = v[g * GB + i];
+                        k_from_r2_vec<KIND == GPX_PERIODIC ? GPX_RBF : KIND, GB>(w, scale);
+#pragma unroll
+                        for (int i = 0; i < GB; ++i) v[g * GB + i] = w[i];
                     }
                 }
+#pragma unroll
+                for (int i = 0; i < GEN; ++i) {
+                    const int kk = g_k0 + i * KSTEP;
+                    const double vv = (c * W_BK + kk < n) ? v[i] : 0.0;
+                    dst[kk * C::LDK] = vv;
+                    if (do_mean) macc = fma(vv, al[i], macc);
+                }
+                mbar_arrive(bar_full + 8 * st);
             }
         }
         cp_async_wait<0>();
-        // column sums of squares of this row block's V fragments
+        smean[pt] = macc;
+    } else {
+        // =========================== CONSUMERS ===========================
+        asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;\n" ::"n"(W_REGS_CONS));
+        const int wm = warp / WN, wn = warp % WN;
+        const int lr = lane >> 2, lc = lane & 3;
+        // swizzled A-fragment offsets: row = 8 f + lr, 16-byte chunk (2 ks + lc/2) ^ lr
+        int offA[W_BK / 4];
 #pragma unroll
-        for (int ni = 0; ni < P_NF; ++ni) {
-            double p0 = 0.0, p1 = 0.0;
+        for (int ks = 0; ks < W_BK / 4; ++ks)
+            offA[ks] = (wm * 8 + lr) * W_BK + ((((ks << 1) | (lc >> 1)) ^ lr) << 1) + (lc & 1);
+        const int offB = lc * C::LDK + wn * 32 + lr;
+        uint32_t it = 0;
+        for (int rb = 0; rb < NRB; ++rb) {
+            const int kd0 = rb * C::R;
+            const int kend = (n < kd0 + C::R) ? n : kd0 + C::R;
+            const int nsl = (kend + W_BK - 1) / W_BK;
+            const int nsl_full = kd0 / W_BK;
+            // fragments that hold rows < n in this block: f < fr_lim  <=>  mi < mi_lim
+            const int fr_lim = (kend - kd0 + 7) >> 3;
+            const int mi_lim = (fr_lim - wm + WM - 1) / WM;
+            double acc[8][4][2];
 #pragma unroll
-            for (int mi = 0; mi < P_MF; ++mi) {
-                p0 = fma(acc[mi][ni][0], acc[mi][ni][0], p0);
-                p1 = fma(acc[mi][ni][1], acc[mi][ni][1], p1);
+            for (int mi = 0; mi < 8; ++mi)
+#pragma unroll
+                for (int ni = 0; ni < 4; ++ni) acc[mi][ni][0] = acc[mi][ni][1] = 0.0;
+
+            for (int c = 0; c < nsl; ++c, ++it) {
+                const uint32_t st = it % C::NST, ph = (it / C::NST) & 1;
+                mbar_wait(bar_full + 8 * st, ph);
+                const double *cW = sW + (size_t)st * C::W_STAGE;
+                const double *cK = sK + (size_t)st * C::K_STAGE + offB;
+                if (c < nsl_full && mi_lim >= 8) {
+#pragma unroll
+                    for (int ks = 0; ks < W_BK / 4; ++ks) {
+                        double a[8], b[4];
+#pragma unroll
+                        for (int ni = 0; ni < 4; ++ni) b[ni] = cK[ks * 4 * C::LDK + ni * 8];
+#pragma unroll
+                        for (int mi = 0; mi < 8; ++mi) a[mi] = cW[mi * (WM * 8 * W_BK) + offA[ks]];
+#pragma unroll
+                        for (int mi = 0; mi < 8; ++mi)
+#pragma unroll
+                            for (int ni = 0; ni < 4; ++ni)
+                                dmma884(acc[mi][ni][0], acc[mi][ni][1], a[mi], b[ni]);
+                    }
+                } else {
+                    // diagonal / ragged block: fragment f = wm + WM*mi is needed for
+                    // k-steps starting below 8*(f+1)
+                    const int kl = c * W_BK - kd0;
+#pragma unroll
+                    for (int ks = 0; ks < W_BK / 4; ++ks) {
+                        const int fmin = (kl + ks * 4) >> 3;                 // may be negative
+                        int mi0 = (fmin - wm + WM - 1) / WM;
+                        mi0 = (fmin - wm) <= 0 ? 0 : mi0;
+                        if (mi0 >= mi_lim) continue;
+                        double b[4];
+#pragma unroll
+                        for (int ni = 0; ni < 4; ++ni) b[ni] = cK[ks * 4 * C::LDK + ni * 8];
+#pragma unroll
+                        for (int mi = 0; mi < 8; ++mi) {
+                            if (mi >= mi0 && mi < mi_lim) {
+                                const double a = cW[mi * (WM * 8 * W_BK) + offA[ks]];
+#pragma unroll
+                                for (int ni = 0; ni < 4; ++ni)
+                                    dmma884(acc[mi][ni][0], acc[mi][ni][1], a, b[ni]);
+                            }
+                        }
+                    }
+                }
+                __syncwarp();
+                if (lane == 0) mbar_arrive(bar_empty + 8 * st);
             }
+            // column sums of squares of this row block's V fragments
 #pragma unroll
-            for (int o = 4; o < 32; o <<= 1) {
-                p0 += __shfl_xor_sync(0xffffffffu, p0, o);
-                p1 += __shfl_xor_sync(0xffffffffu, p1, o);
-            }
-            if (lr == 0) {
-                wpart[wm * C::MT + wn * 32 + ni * 8 + lc * 2] = p0;
-                wpart[wm * C::MT + wn * 32 + ni * 8 + lc * 2 + 1] = p1;
-            }
-        }
-        __syncthreads();
-        if (t < C::MT) {
-            double a2 = colsum[t];
+            for (int ni = 0; ni < 4; ++ni) {
+                double p0 = 0.0, p1 = 0.0;
 #pragma unroll
-            for (int w = 0; w < WM; ++w) a2 += wpart[w * C::MT + t];
-            colsum[t] = a2;
+                for (int mi = 0; mi < 8; ++mi) {
+                    p0 = fma(acc[mi][ni][0], acc[mi][ni][0], p0);
+                    p1 = fma(acc[mi][ni][1], acc[mi][ni][1], p1);
+                }
+#pragma unroll
+                for (int o = 4; o < 32; o <<= 1) {
+                    p0 += __shfl_xor_sync(0xffffffffu, p0, o);
+                    p1 += __shfl_xor_sync(0xffffffffu, p1, o);
+                }
+                if (lr == 0) {
+                    wpart[wm * C::MT + wn * 32 + ni * 8 + lc * 2] = p0;
+                    wpart[wm * C::MT + wn * 32 + ni * 8 + lc * 2 + 1] = p1;
+                }
+            }
+            consumer_bar_sync();
+            if (t < C::MT) {
+                double a2 = colsum[t];
+#pragma unroll
+                for (int w = 0; w < WM; ++w) a2 += wpart[w * C::MT + t];
+                colsum[t] = a2;
+            }
+            consumer_bar_sync();
         }
     }
-
-    // mean: add the partial dot products of the threads that share a candidate
-    smean[t] = macc;
     __syncthreads();
     if (t < C::MT) {
         const int gj = j0 + t;
         if (gj < M) {
-            double kd = (KIND == GPX_PERIODIC) ? scale : k_from_r2<KIND == GPX_PERIODIC ? GPX_RBF : KIND>(0.0, scale);
+            const double kd = (KIND == GPX_PERIODIC)
+                                  ? scale
+                                  : k_from_r2 < KIND == GPX_PERIODIC ? GPX_RBF : KIND > (0.0, scale);
             if (var) var[(size_t)s * M + gj] = (kd + diag_add[s]) - colsum[t];
             if (mu) {
-                double m0 = m_new ? m_new[(size_t)s * M + gj] : m_const;
+                const double m0 = m_new ? m_new[(size_t)s * M + gj] : m_const;
                 double dot = 0.0;
-                for (int q = t; q < P_THREADS; q += C::MT) dot += smean[q];
+                for (int q = t; q < W_PROD_THREADS; q += C::MT) dot += smean[q];
                 mu[(size_t)s * M + gj] = m0 + dot;
             }
         }
     }
 }
 
-template <int KIND, int WM, int WN, int BK>
-static int launch_predict(const gpx_kernel_params *kp, int64_t S, int64_t n, int64_t M,
-                          const double *x, const double *xnew, const double *W, int64_t ldw,
-                          const double *alpha, const double *m_new, double m_const,
-                          const double *diag_add, double *mu, double *var, cudaStream_t st) {
-    using C = PCfg<WM, WN, BK>;
-    const size_t smem = C::SMEM_DOUBLES * sizeof(double);
+// ---------------------------------------------------------------------------
+// host side
+// ---------------------------------------------------------------------------
+typedef CUresult (*encode_tiled_fn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *,
+                                    const cuuint64_t *, const cuuint64_t *, const cuuint32_t *,
+                                    const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                    CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static encode_tiled_fn get_encode_tiled() {
+    static encode_tiled_fn fn = nullptr;
+    if (!fn) {
+        void *p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) ==
+                cudaSuccess &&
+            q == cudaDriverEntryPointSuccess)
+            fn = (encode_tiled_fn)p;
+    }
+    return fn;
+}
+
+// 3-D view of W [S, n, ldw] (fp64): dims (k, row, sample); box (16, box_rows, 1); 128-byte swizzle
+static int make_w_tensormap(CUtensorMap *tm, const double *W, int64_t S, int64_t n, int64_t ldw,
+                            int box_rows) {
+    encode_tiled_fn enc = get_encode_tiled();
+    if (!enc) { set_error("gpx_predict: cuTensorMapEncodeTiled unavailable"); return 999; }
+    cuuint64_t dims[3] = {(cuuint64_t)n, (cuuint64_t)n, (cuuint64_t)S};
+    cuuint64_t strides[2] = {(cuuint64_t)ldw * 8, (cuuint64_t)n * ldw * 8};
+    cuuint32_t box[3] = {(cuuint32_t)W_BK, (cuuint32_t)box_rows, 1};
+    cuuint32_t estr[3] = {1, 1, 1};
+    CUresult r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 3, (void *)W, dims, strides, box, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                     CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) { set_error("gpx_predict: cuTensorMapEncodeTiled failed (%d)", (int)r); return 999; }
+    return 0;
+}
+
+template <int KIND, int WM, int WN>
+static int launch_predict_ws(const gpx_kernel_params *kp, int64_t S, int64_t n, int64_t M,
+                             const double *xs, const double *xnew, const double *W, int64_t ldw,
+                             const double *m_new, double m_const, const double *diag_add,
+                             double *mu, double *var, cudaStream_t st) {
+    using C = WCfg<WM, WN>;
     static bool configured = false;
     if (!configured) {
-        cudaError_t e = cudaFuncSetAttribute(predict_kernel<KIND, WM, WN, BK>,
-                                             cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        cudaError_t e = cudaFuncSetAttribute(predict_ws_kernel<KIND, WM, WN>,
+                                             cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             (int)C::SMEM_BYTES);
         if (e != cudaSuccess) { set_error("gpx_predict: smem attribute failed (%d)", (int)e); return (int)e; }
         configured = true;
     }
+    CUtensorMap tm;
+    int rc = make_w_tensormap(&tm, W, S, n, ldw, C::BOX_ROWS);
+    if (rc) return rc;
     dim3 grid((unsigned)((M + C::MT - 1) / C::MT), (unsigned)S);
-    predict_kernel<KIND, WM, WN, BK><<<grid, P_THREADS, smem, st>>>(
-        *kp, (int)n, (int)M, x, xnew, W, ldw, alpha, m_new, m_const, diag_add, mu, var);
+    predict_ws_kernel<KIND, WM, WN><<<grid, W_THREADS, C::SMEM_BYTES, st>>>(
+        tm, *kp, (int)n, (int)M, xs, xnew, m_new, m_const, diag_add, mu, var);
     return 0;
 }
 
@@ -309,24 +473,35 @@ template <int KIND>
 static int dispatch_predict(const gpx_kernel_params *kp, int64_t S, int64_t n, int64_t M,
                             const double *x, const double *xnew, const double *W, int64_t ldw,
                             const double *alpha, const double *m_new, double m_const,
-                            const double *diag_add, double *mu, double *var, cudaStream_t st) {
-    // tall slabs amortise the K* regeneration for large n; wide candidate tiles
-    // suit small n (the whole W fits one slab)
+                            const double *diag_add, double *mu, double *var, double *ws,
+                            cudaStream_t st) {
+    // small n: the whole W fits one slab and the work is K*-generation bound
     if (n <= 64)
         return launch_predict<KIND, 1, 8, 16>(kp, S, n, M, x, xnew, W, ldw, alpha, m_new, m_const, diag_add, mu, var, st);
     if (n <= 128)
         return launch_predict<KIND, 2, 4, 16>(kp, S, n, M, x, xnew, W, ldw, alpha, m_new, m_const, diag_add, mu, var, st);
+    if (!ws) { set_error("gpx_predict: workspace required for n > 128"); return -16; }
+    dim3 g((unsigned)((n + 255) / 256), (unsigned)S);
+    predict_prep_kernel<KIND><<<g, 256, 0, st>>>(*kp, (int)n, x, alpha, ws);
+    count_launches(1);
+    // tall slabs amortise the K* regeneration for large n
     if (n <= 512)
-        return launch_predict<KIND, 4, 2, 16>(kp, S, n, M, x, xnew, W, ldw, alpha, m_new, m_const, diag_add, mu, var, st);
-    return launch_predict<KIND, 8, 1, 8>(kp, S, n, M, x, xnew, W, ldw, alpha, m_new, m_const, diag_add, mu, var, st);
+        return launch_predict_ws<KIND, 4, 2>(kp, S, n, M, ws, xnew, W, ldw, m_new, m_const, diag_add, mu, var, st);
+    return launch_predict_ws<KIND, 8, 1>(kp, S, n, M, ws, xnew, W, ldw, m_new, m_const, diag_add, mu, var, st);
 }
 
 }  // namespace gpx
 
+extern "C" size_t gpx_predict_ws_bytes(int64_t S, int64_t n, int32_t d) {
+    if (n <= 128 || S <= 0) return 0;
+    return (size_t)S * (size_t)n * (size_t)(d + 2) * sizeof(double);
+}
+
 extern "C" int gpx_predict(const gpx_kernel_params *kp, int64_t S, int64_t n, int64_t M,
                            const double *x, const double *xnew, const double *W, int64_t ldw,
                            const double *alpha, const double *m_new, double m_const,
-                           const double *diag_add, double *mu, double *var, void *stream) {
+                           const double *diag_add, double *mu, double *var, void *ws,
+                           void *stream) {
     using namespace gpx;
     GPX_ARG_CHECK(validate_kp(kp) == 0, 1);
     GPX_ARG_CHECK(S >= 0 && S <= 65535, 2);
@@ -336,20 +511,22 @@ extern "C" int gpx_predict(const gpx_kernel_params *kp, int64_t S, int64_t n, in
     GPX_ARG_CHECK(xnew != nullptr || M == 0, 6);
     GPX_ARG_CHECK(W != nullptr || S * n == 0, 7);
     GPX_ARG_CHECK(ldw >= n && (ldw % 2 == 0), 8);
+    GPX_ARG_CHECK(((uintptr_t)W & 15) == 0, 7);
     GPX_ARG_CHECK(alpha != nullptr || S * n == 0, 9);
     GPX_ARG_CHECK(diag_add != nullptr || S == 0, 12);
+    GPX_ARG_CHECK(ws != nullptr || gpx_predict_ws_bytes(S, n, kp->d) == 0, 15);
     if (S == 0 || M == 0) return 0;
     cudaStream_t st = (cudaStream_t)stream;
     int rc;
     switch (kp->kind) {
         case GPX_RBF:
-            rc = dispatch_predict<GPX_RBF>(kp, S, n, M, x, xnew, W, ldw, alpha, m_new, m_const, diag_add, mu, var, st);
+            rc = dispatch_predict<GPX_RBF>(kp, S, n, M, x, xnew, W, ldw, alpha, m_new, m_const, diag_add, mu, var, (double *)ws, st);
             break;
         case GPX_MATERN52:
-            rc = dispatch_predict<GPX_MATERN52>(kp, S, n, M, x, xnew, W, ldw, alpha, m_new, m_const, diag_add, mu, var, st);
+            rc = dispatch_predict<GPX_MATERN52>(kp, S, n, M, x, xnew, W, ldw, alpha, m_new, m_const, diag_add, mu, var, (double *)ws, st);
             break;
         default:
-            rc = dispatch_predict<GPX_PERIODIC>(kp, S, n, M, x, xnew, W, ldw, alpha, m_new, m_const, diag_add, mu, var, st);
+            rc = dispatch_predict<GPX_PERIODIC>(kp, S, n, M, x, xnew, W, ldw, alpha, m_new, m_const, diag_add, mu, var, (double *)ws, st);
             break;
     }
     if (rc) return rc;

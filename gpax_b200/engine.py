@@ -158,17 +158,24 @@ def mll_grad(hpd: HyperParams, x, W, alpha):
     return out
 
 
+def predict_ws_alloc(S, n, d, dev):
+    nbytes = lib.gpx_predict_ws_bytes(S, n, d)
+    return torch.empty(max(1, nbytes // 8), dtype=F64, device=dev)
+
+
 def predict(hpd: HyperParams, x, x_new, W, alpha, diag_add, m_new=None, m_const=1.0,
-            want_mu=True, want_var=True, mu=None, var=None):
+            want_mu=True, want_var=True, mu=None, var=None, ws=None):
     S, n, M = hpd.S, x.shape[0], x_new.shape[0]
     dev = x.device
+    if ws is None:
+        ws = predict_ws_alloc(S, n, hpd.d, dev)
     if want_mu and mu is None:
         mu = torch.empty((S, M), dtype=F64, device=dev)
     if want_var and var is None:
         var = torch.empty((S, M), dtype=F64, device=dev)
     check(lib.gpx_predict(C.byref(hpd.kp), S, n, M, _ptr(x), _ptr(x_new), _ptr(W), W.shape[2],
                           _ptr(alpha), _ptr(m_new), float(m_const), _ptr(diag_add), _ptr(mu),
-                          _ptr(var), _stream()), "gpx_predict")
+                          _ptr(var), _ptr(ws), _stream()), "gpx_predict")
     return mu, var
 
 

@@ -37,7 +37,7 @@
 extern "C" {
 #endif
 
-#define GPX_ABI_VERSION 1
+#define GPX_ABI_VERSION 2
 
 /* covariance families: gpax/kernels.py:110 (RBF), :129 (Matern nu=5/2), :150 (Periodic) */
 enum { GPX_RBF = 0, GPX_MATERN52 = 1, GPX_PERIODIC = 2 };
@@ -139,12 +139,15 @@ int gpx_mll_grad(const gpx_kernel_params *kp, int64_t S, int64_t n, const double
  *   m_new [S,M] or NULL (-> m_const, ConstantMean gpax/means.py:75-78);
  *   diag_add [S]: (k_noise if observation_noise else 0) + k_jitter (gpax/gp.py:283-287);
  *   mu, var [S, M] out (either nullable).
+ *   ws: gpx_predict_ws_bytes(S, n, d) bytes of scratch (the per-sample scaled
+ *   training inputs; 0 bytes / NULL allowed for n <= 128).
  */
+size_t gpx_predict_ws_bytes(int64_t S, int64_t n, int32_t d);
 int gpx_predict(const gpx_kernel_params *kp, int64_t S, int64_t n, int64_t M,
                 const double *x, const double *xnew,
                 const double *W, int64_t ldw, const double *alpha,
                 const double *m_new, double m_const, const double *diag_add,
-                double *mu, double *var, void *stream);
+                double *mu, double *var, void *ws, void *stream);
 
 /* ---------------------------------------------------------------------------
  * gpx_acq_reduce: mixture moments over S (fixed order s = 0..S-1), reverse

@@ -101,8 +101,8 @@ def test_potrf_flags_non_spd(cuda):
 
 
 @pytest.mark.parametrize("kind,per", KINDS)
-@pytest.mark.parametrize("n,d,S,M", [(64, 1, 9, 200), (100, 2, 5, 333), (300, 3, 4, 150),
-                                     (640, 2, 3, 100)])
+@pytest.mark.parametrize("n,d,S,M", [(64, 1, 9, 200), (100, 2, 5, 333), (129, 1, 3, 65), (300, 3, 4, 150),
+                                     (512, 2, 2, 64), (640, 2, 3, 100), (1100, 2, 2, 77)])
 def test_predict_matches_oracle(cuda, kind, per, n, d, S, M):
     """Per-sample mean and variance vs the reference's Cholesky branch
     (gpax/gp.py:295-301): 1e-10 relative (normwise, max-norm)."""
