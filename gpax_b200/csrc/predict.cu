@@ -5,19 +5,25 @@
 //     mu[s,j]  = m_new[s,j] + k*_j . alpha_s
 //     var[s,j] = k(x*_j,x*_j) + diag_add[s] - || W_s k*_j ||^2 ,  W_s = L_s^-1
 //
-// Large-n kernel (n > 128): warp-specialised, one CTA per (sample s, tile of MT
-// candidates), 12 warps:
-//   * warps 0-7  CONSUMERS: FP64 DMMA (mma.sync m8n8k4) over a slab of R rows of
-//     W_s times the K*^T slice, accumulators in registers, then the column sums
-//     of squares of V = W K*^T (V is never stored).
-//   * warps 8-11 PRODUCERS: one elected thread streams the W slab of each
-//     16-column slice with TMA (cp.async.bulk.tensor, 128-byte swizzle, the
-//     layout the DMMA A-fragment loads read conflict-free); all 128 threads
-//     generate the K*^T slice on chip (reference operation order: divide by the
-//     length scale, norms, X2 - 2XZ + Z2, clip; gpax/kernels.py:39-51) and
-//     accumulate the mean k*.alpha.  K* never touches HBM (north_star item 3).
-//   Stages are handed over through full/empty mbarriers; registers are moved
-//   from the producer to the consumer warpgroups with setmaxnreg.
+// Large-n kernel (n > 128): one CTA per (sample s, tile of MT candidates), 8 warps.
+//   Every warp generates its share of the K*^T slice two slices ahead
+//   (reference operation order: divide by the length scale, norms,
+//   X2 - 2XZ + Z2, clip; gpax/kernels.py:39-51; straight-line N-wide exp/sqrt)
+//   in the SAME instruction stream as its FP64 DMMAs (mma.sync m8n8k4) over a
+//   slab of R rows of W_s times the current K*^T slice; accumulators stay in
+//   registers and only the column sums of squares of V = W K*^T leave them
+//   (V is never stored).  K* never touches HBM (north_star item 3).
+//   The W slab of each 16-column slice is streamed by TMA (cp.async.bulk.tensor,
+//   128-byte swizzle -- the layout the DMMA A-fragment loads read conflict-free),
+//   issued by one elected thread as soon as the target stage is released.
+//   Stages are handed over through fullW / fullK / empty mbarriers; there is no
+//   CTA-wide barrier in the main loop.
+//   Why generation lives in the DMMA warps: on B200 the FP64 ALU and DMMA share
+//   one pipe per SM sub-partition and pending DMMAs always win arbitration
+//   (measured with tools/probe/pipe_probe.cu: a DFMA warp next to two DMMA
+//   warps makes no progress until they drain), so dedicated generator warps
+//   starve; inside the DMMA warps the generator's DFMAs are issued in program
+//   order between the warp's own DMMAs.
 // W is lower triangular: row blocks are walked top to bottom, only k-steps at
 // or below the diagonal of each 8-row fragment are issued (warp-uniform
 // branches), and fragments are dealt cyclically to the warps so the triangular
@@ -30,17 +36,16 @@
 
 namespace gpx {
 
-constexpr int W_CONS_WARPS = 8;
-constexpr int W_PROD_WARPS = 4;
-constexpr int W_THREADS = (W_CONS_WARPS + W_PROD_WARPS) * 32;   // 384
-constexpr int W_PROD_THREADS = W_PROD_WARPS * 32;               // 128
+constexpr int W_MATH_WARPS = 8;                                 // K* generation + DMMA
+constexpr int W_MATH_THREADS = W_MATH_WARPS * 32;               // 256
+constexpr int W_THREADS = W_MATH_THREADS;                       // 256 (up to 255 regs/thread)
 constexpr int W_BK = 16;                                        // 128-byte rows = one swizzle span
-constexpr int W_REGS_CONS = 208, W_REGS_PROD = 88;              // 256*208 + 128*88 = 384*168
+constexpr int W_GEN_AHEAD = 2;                                  // K* slices are generated this many slices ahead
 constexpr int W_XS = GPX_MAX_D + 2;                             // staged training row: coords, norm, alpha
 
 template <int WM, int WN>
 struct WCfg {
-    static_assert(WM * WN == W_CONS_WARPS, "8 consumer warps");
+    static_assert(WM * WN == W_MATH_WARPS, "8 math warps");
     static constexpr int R = WM * 64;          // W rows per pass
     static constexpr int MT = WN * 32;         // candidates per CTA
     static constexpr int NST = (R >= 512) ? 3 : 4;
@@ -49,12 +54,15 @@ struct WCfg {
     static constexpr int K_STAGE = W_BK * LDK;
     static constexpr int BOX_ROWS = (R > 256) ? 256 : R;
     static constexpr int NBOX = R / BOX_ROWS;
+    static constexpr int KSTEP = W_MATH_THREADS / MT;   // k rows generated per pass over the slice
+    static constexpr int GEN = W_BK / KSTEP;            // K* entries per thread per slice
+    static_assert(KSTEP >= 1 && KSTEP * GEN == W_BK, "generator mapping");
     static constexpr size_t SMEM_BYTES =
         1024 /*alignment slack*/ +
         sizeof(double) * ((size_t)NST * W_STAGE + (size_t)NST * K_STAGE + MT * (GPX_MAX_D + 1) +
-                          MT /*colsum*/ + WM * MT /*wpart*/ + W_PROD_THREADS /*smean*/ +
-                          2 * GPX_MAX_D + W_PROD_WARPS * 2 * W_BK * W_XS /*sXW (upper bound)*/) +
-        sizeof(uint64_t) * 2 * NST;
+                          MT /*colsum*/ + WM * MT /*wpart*/ + W_MATH_THREADS /*smean*/ +
+                          2 * GPX_MAX_D + W_MATH_WARPS * 2 * GEN * W_XS /*sXW*/) +
+        sizeof(uint64_t) * 3 * NST;
 };
 
 // ---- mbarrier / TMA primitives (PTX) ---------------------------------------
@@ -88,8 +96,8 @@ __device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap *tm,
         "[%0], [%1, {%3, %4, %5}], [%2];\n" ::"r"(dst), "l"(tm), "r"(bar), "r"(c0), "r"(c1), "r"(c2)
         : "memory");
 }
-__device__ __forceinline__ void consumer_bar_sync() {
-    asm volatile("bar.sync 1, %0;\n" ::"n"(W_CONS_WARPS * 32) : "memory");
+__device__ __forceinline__ void math_bar_sync() {
+    asm volatile("bar.sync 1, %0;\n" ::"n"(W_MATH_THREADS) : "memory");
 }
 
 // ---------------------------------------------------------------------------
@@ -119,6 +127,10 @@ predict_prep_kernel(gpx_kernel_params kp, int n, const double *__restrict__ x,
 // ---------------------------------------------------------------------------
 // main kernel
 // ---------------------------------------------------------------------------
+struct SliceIter {
+    int rb, c, nsl;
+};
+
 template <int KIND, int WM, int WN>
 __global__ void __launch_bounds__(W_THREADS, 1)
 predict_ws_kernel(const __grid_constant__ CUtensorMap tmW, gpx_kernel_params kp, int n, int M,
@@ -136,18 +148,19 @@ predict_ws_kernel(const __grid_constant__ CUtensorMap tmW, gpx_kernel_params kp,
     double *sZ = sK + (size_t)C::NST * C::K_STAGE;        // [MT][MAX_D+1]
     double *colsum = sZ + C::MT * (GPX_MAX_D + 1);        // [MT]
     double *wpart = colsum + C::MT;                       // [WM][MT]
-    double *smean = wpart + WM * C::MT;                   // [W_PROD_THREADS]
-    double *s_len = smean + W_PROD_THREADS;               // [MAX_D]
+    double *smean = wpart + WM * C::MT;                   // [W_MATH_THREADS]
+    double *s_len = smean + W_MATH_THREADS;               // [MAX_D]
     double *s_per = s_len + GPX_MAX_D;                    // [MAX_D]
-    double *sXW = s_per + GPX_MAX_D;                      // [W_PROD_WARPS][2][GEN][W_XS]
-    uint64_t *bars = reinterpret_cast<uint64_t *>(sXW + W_PROD_WARPS * 2 * W_BK * W_XS);   // full[NST], empty[NST]
+    double *sXW = s_per + GPX_MAX_D;                      // [W_MATH_WARPS][2][GEN][W_XS]
+    uint64_t *bars = reinterpret_cast<uint64_t *>(sXW + W_MATH_WARPS * 2 * C::GEN * W_XS);
 
     const int s = blockIdx.y;
     const int j0 = blockIdx.x * C::MT;
     const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
     const int d = kp.d;
     const double scale = kp.scale[s];
-    const uint32_t bar_full = smem_u32(bars), bar_empty = smem_u32(bars + C::NST);
+    const uint32_t bar_fullW = smem_u32(bars), bar_fullK = smem_u32(bars + C::NST),
+                   bar_empty = smem_u32(bars + 2 * C::NST);
 
     if (t < d) {
         s_len[t] = len_of(kp, s, t);
@@ -157,8 +170,9 @@ predict_ws_kernel(const __grid_constant__ CUtensorMap tmW, gpx_kernel_params kp,
     if (t == 0) {
 #pragma unroll
         for (int i = 0; i < C::NST; ++i) {
-            mbar_init(bar_full + 8 * i, W_PROD_THREADS + 1);   // producers + the expect_tx arrive
-            mbar_init(bar_empty + 8 * i, W_CONS_WARPS);        // one elected lane per consumer warp
+            mbar_init(bar_fullW + 8 * i, 1);               // the expect_tx arrive of the TMA thread
+            mbar_init(bar_fullK + 8 * i, W_MATH_WARPS);    // one elected lane per math warp
+            mbar_init(bar_empty + 8 * i, W_MATH_WARPS);
         }
         asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
         asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory");
@@ -180,23 +194,34 @@ predict_ws_kernel(const __grid_constant__ CUtensorMap tmW, gpx_kernel_params kp,
     __syncthreads();
 
     const int NRB = (n + C::R - 1) / C::R;
+    auto nsl_of = [&](int rb) {
+        const int kend = (n < (rb + 1) * C::R) ? n : (rb + 1) * C::R;
+        return (kend + W_BK - 1) / W_BK;
+    };
+    auto advance = [&](SliceIter &it) {
+        if (++it.c == it.nsl) {
+            ++it.rb;
+            it.c = 0;
+            it.nsl = it.rb < NRB ? nsl_of(it.rb) : 1;
+        }
+    };
+    int T = 0;
+    for (int rb = 0; rb < NRB; ++rb) T += nsl_of(rb);
 
-    if (warp >= W_CONS_WARPS) {
-        // =========================== PRODUCERS ===========================
-        asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;\n" ::"n"(W_REGS_PROD));
-        const int pt = t - W_CONS_WARPS * 32;                    // 0..127
-        const int pw = pt >> 5;
-        constexpr int KSTEP = W_PROD_THREADS / C::MT;            // k rows generated per pass
-        constexpr int GEN = W_BK / KSTEP;                        // elements per thread per slice
-        static_assert(KSTEP >= 1 && KSTEP * GEN == W_BK, "producer mapping");
-        const int g_j = pt % C::MT, g_k0 = pt / C::MT;           // g_k0 is warp-uniform
+    {
+        // ===================== math warps: K* generation + DMMA =====================
+        constexpr int KSTEP = C::KSTEP, GEN = C::GEN, D = W_GEN_AHEAD;
+        const int wm = warp / WN, wn = warp % WN;
+        const int lr = lane >> 2, lc = lane & 3;
+        // ---- generator state: thread -> candidate g_j, k rows g_k0 + i*KSTEP ----
+        const int g_j = t % C::MT, g_k0 = t / C::MT;             // g_k0 is warp-uniform
         const double *pz = sZ + g_j * (GPX_MAX_D + 1);
         const int XS = d + 2;
         const double *xs_s = xs + (size_t)s * n * XS;
         const double z2n = pz[GPX_MAX_D];
         // warp-private double buffer of the GEN staged training rows of a slice
         // (scaled coordinates, norm, alpha), prefetched one slice ahead with cp.async
-        double *xw = sXW + pw * (2 * GEN * W_XS);
+        double *xw = sXW + warp * (2 * GEN * W_XS);
         int cp_i[3], cp_col[3];
 #pragma unroll
         for (int e = 0; e < 3; ++e) {
@@ -216,180 +241,204 @@ predict_ws_kernel(const __grid_constant__ CUtensorMap tmW, gpx_kernel_params kp,
             }
             cp_async_commit();
         };
+        int gi = 0;                                   // next slice to generate
+        SliceIter git{0, 0, nsl_of(0)};
         double macc = 0.0;
-        uint32_t it = 0;
         prefetch_rows(0, 0);
-        for (int rb = 0; rb < NRB; ++rb) {
-            const int kd0 = rb * C::R;
-            const int kend = (n < kd0 + C::R) ? n : kd0 + C::R;
-            const int nsl = (kend + W_BK - 1) / W_BK;
-            const bool do_mean = (rb == NRB - 1);
-            for (int c = 0; c < nsl; ++c, ++it) {
-                const uint32_t st = it % C::NST, ph = (it / C::NST) & 1;
-                const int buf = it & 1;
-                __syncwarp();                                    // everyone is done with buf ^ 1
-                prefetch_rows((c + 1 < nsl) ? c + 1 : 0, buf ^ 1);   // next slice (or first of next pass)
-                mbar_wait(bar_empty + 8 * st, ph ^ 1);
-                if (pt == 0) {
-                    mbar_arrive_expect_tx(bar_full + 8 * st, (uint32_t)(C::W_STAGE * sizeof(double)));
+        // gen_begin: distances of this thread's GEN entries of slice gi (registers only)
+        auto gen_begin = [&](double (&v)[GEN], double (&al)[GEN]) {
+            const int buf = gi & 1;
+            __syncwarp();                             // everyone is done with buf ^ 1
+            SliceIter nx = git;
+            advance(nx);
+            prefetch_rows(nx.rb < NRB ? nx.c : 0, buf ^ 1);
+            cp_async_wait<1>();
+            __syncwarp();                             // the warp's rows of slice gi landed
+            const double *rows = xw + buf * GEN * W_XS;
 #pragma unroll
-                    for (int b = 0; b < C::NBOX; ++b)
-                        tma_load_3d(smem_u32(sW + (size_t)st * C::W_STAGE + b * C::BOX_ROWS * W_BK),
-                                    &tmW, bar_full + 8 * st, c * W_BK, kd0 + b * C::BOX_ROWS, s);
+            for (int i = 0; i < GEN; ++i) {
+                const double *px = rows + i * W_XS;
+                if (KIND == GPX_PERIODIC) {
+                    double acc = 0.0;
+                    for (int q = 0; q < d; ++q) {
+                        double df = pz[q] - px[q];
+                        double sn = sin(GPX_PI * df / s_per[q]) / s_len[q];
+                        acc += sn * sn;
+                    }
+                    v[i] = acc;                        // exponent / -2
+                } else {
+                    double xz = 0.0;
+                    for (int q = 0; q < d; ++q) xz = fma(pz[q], px[q], xz);
+                    v[i] = fmax((z2n - 2.0 * xz) + px[d], 0.0);
                 }
-                cp_async_wait<1>();
-                __syncwarp();                                    // the warp's rows of slice c landed
-                const double *rows = xw + buf * GEN * W_XS;
-                double *dst = sK + (size_t)st * C::K_STAGE + g_j;
-                double v[GEN], al[GEN];
+                al[i] = px[d + 1];
+            }
+        };
+        // gen_math: straight-line N-wide exp / sqrt (common.cuh) so that the compiler
+        // can interleave it with the DMMA stream of the same warp
+        auto gen_math = [&](double (&v)[GEN]) {
+            constexpr int GB = GEN < 4 ? GEN : 4;
+#pragma unroll
+            for (int g = 0; g < GEN / GB; ++g) {
+                double w[GB];
+#pragma unroll
+                for (int i = 0; i < GB; ++i) w[i] = v[g * GB + i];
                 if (KIND == GPX_PERIODIC) {
 #pragma unroll
-                    for (int i = 0; i < GEN; ++i) {
-                        const double *px = rows + i * W_XS;
-                        double acc = 0.0;
-                        for (int q = 0; q < d; ++q) {
-                            double df = pz[q] - px[q];
-                            double sn = sin(GPX_PI * df / s_per[q]) / s_len[q];
-                            acc += sn * sn;
-                        }
-                        v[i] = -2.0 * acc;
-                        al[i] = px[d + 1];
-                    }
-#pragma unroll
-                    for (int i = 0; i < GEN; ++i) v[i] = scale * exp(v[i]);
+                    for (int i = 0; i < GB; ++i) w[i] = 4.0 * w[i];   // exp(-2a) = rbf form exp(-0.5 * 4a)
+                    k_from_r2_vec<GPX_RBF, GB>(w, scale);
                 } else {
-#pragma unroll
-                    for (int i = 0; i < GEN; ++i) {
-                        const double *px = rows + i * W_XS;
-                        double xz = 0.0;
-                        for (int q = 0; q < d; ++q) xz = fma(pz[q], px[q], xz);
-                        v[i] = fmax((z2n - 2.0 * xz) + px[d], 0.0);
-                        al[i] = px[d + 1];
-                    }
-                    // N-wide straight-line exp/sqrt so the chains interleave (common.cuh)
-                    constexpr int GB = GEN < 4 ? GEN : 4;
-#pragma unroll
-                    for (int g = 0; g < GEN / GB; ++g) {
-                        double w[GB];
-#pragma unroll
-                        for (int i = 0; i < GB; ++i) w[i] = v[g * GB + i];
-                        k_from_r2_vec<KIND == GPX_PERIODIC ? GPX_RBF : KIND, GB>(w, scale);
-#pragma unroll
-                        for (int i = 0; i < GB; ++i) v[g * GB + i] = w[i];
-                    }
+                    k_from_r2_vec<KIND == GPX_PERIODIC ? GPX_RBF : KIND, GB>(w, scale);
                 }
 #pragma unroll
-                for (int i = 0; i < GEN; ++i) {
-                    const int kk = g_k0 + i * KSTEP;
-                    const double vv = (c * W_BK + kk < n) ? v[i] : 0.0;
-                    dst[kk * C::LDK] = vv;
-                    if (do_mean) macc = fma(vv, al[i], macc);
-                }
-                mbar_arrive(bar_full + 8 * st);
+                for (int i = 0; i < GB; ++i) v[g * GB + i] = w[i];
             }
+        };
+        // gen_end: publish the entries into the stage of slice gi
+        auto gen_end = [&](double (&v)[GEN], double (&al)[GEN]) {
+            const uint32_t gst = gi % C::NST, gph = (gi / C::NST) & 1;
+            mbar_wait(bar_empty + 8 * gst, gph ^ 1);
+            if (t == 0) {
+                // the stage is free: stream the W slab of slice gi into it (TMA)
+                mbar_arrive_expect_tx(bar_fullW + 8 * gst, (uint32_t)(C::W_STAGE * sizeof(double)));
+#pragma unroll
+                for (int b = 0; b < C::NBOX; ++b)
+                    tma_load_3d(smem_u32(sW + (size_t)gst * C::W_STAGE + b * C::BOX_ROWS * W_BK), &tmW,
+                                bar_fullW + 8 * gst, git.c * W_BK, git.rb * C::R + b * C::BOX_ROWS, s);
+            }
+            double *dst = sK + (size_t)gst * C::K_STAGE + g_j;
+            const bool do_mean = (git.rb == NRB - 1);
+#pragma unroll
+            for (int i = 0; i < GEN; ++i) {
+                const int kk = g_k0 + i * KSTEP;
+                const double vv = (git.c * W_BK + kk < n) ? v[i] : 0.0;
+                dst[kk * C::LDK] = vv;
+                if (do_mean) macc = fma(vv, al[i], macc);
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(bar_fullK + 8 * gst);
+            ++gi;
+            advance(git);
+        };
+        // prologue: the first D slices
+        for (int q = 0; q < D && gi < T; ++q) {
+            double v[GEN], al[GEN];
+            gen_begin(v, al);
+            gen_math(v);
+            gen_end(v, al);
         }
-        cp_async_wait<0>();
-        smean[pt] = macc;
-    } else {
-        // =========================== CONSUMERS ===========================
-        asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;\n" ::"n"(W_REGS_CONS));
-        const int wm = warp / WN, wn = warp % WN;
-        const int lr = lane >> 2, lc = lane & 3;
+
         // swizzled A-fragment offsets: row = 8 f + lr, 16-byte chunk (2 ks + lc/2) ^ lr
         int offA[W_BK / 4];
 #pragma unroll
         for (int ks = 0; ks < W_BK / 4; ++ks)
             offA[ks] = (wm * 8 + lr) * W_BK + ((((ks << 1) | (lc >> 1)) ^ lr) << 1) + (lc & 1);
         const int offB = lc * C::LDK + wn * 32 + lr;
-        uint32_t it = 0;
-        for (int rb = 0; rb < NRB; ++rb) {
-            const int kd0 = rb * C::R;
+
+        double acc[8][4][2];
+#pragma unroll
+        for (int mi = 0; mi < 8; ++mi)
+#pragma unroll
+            for (int ni = 0; ni < 4; ++ni) acc[mi][ni][0] = acc[mi][ni][1] = 0.0;
+        SliceIter cit{0, 0, nsl_of(0)};
+        for (int i = 0; i < T; ++i) {
+            const int kd0 = cit.rb * C::R;
             const int kend = (n < kd0 + C::R) ? n : kd0 + C::R;
-            const int nsl = (kend + W_BK - 1) / W_BK;
             const int nsl_full = kd0 / W_BK;
             // fragments that hold rows < n in this block: f < fr_lim  <=>  mi < mi_lim
             const int fr_lim = (kend - kd0 + 7) >> 3;
             const int mi_lim = (fr_lim - wm + WM - 1) / WM;
-            double acc[8][4][2];
-#pragma unroll
-            for (int mi = 0; mi < 8; ++mi)
-#pragma unroll
-                for (int ni = 0; ni < 4; ++ni) acc[mi][ni][0] = acc[mi][ni][1] = 0.0;
+            const int c = cit.c;
 
-            for (int c = 0; c < nsl; ++c, ++it) {
-                const uint32_t st = it % C::NST, ph = (it / C::NST) & 1;
-                mbar_wait(bar_full + 8 * st, ph);
-                const double *cW = sW + (size_t)st * C::W_STAGE;
-                const double *cK = sK + (size_t)st * C::K_STAGE + offB;
-                if (c < nsl_full && mi_lim >= 8) {
+            const bool has_g = gi < T;
+            double v[GEN], al[GEN];
 #pragma unroll
-                    for (int ks = 0; ks < W_BK / 4; ++ks) {
-                        double a[8], b[4];
+            for (int q = 0; q < GEN; ++q) v[q] = 0.0, al[q] = 0.0;
+            if (has_g) gen_begin(v, al);
+
+            const uint32_t st = i % C::NST, ph = (i / C::NST) & 1;
+            mbar_wait(bar_fullW + 8 * st, ph);
+            mbar_wait(bar_fullK + 8 * st, ph);
+            const double *cW = sW + (size_t)st * C::W_STAGE;
+            const double *cK = sK + (size_t)st * C::K_STAGE + offB;
+            if (c < nsl_full && mi_lim >= 8) {
+                gen_math(v);        // same basic block as the DMMAs below: interleaved by ptxas
 #pragma unroll
-                        for (int ni = 0; ni < 4; ++ni) b[ni] = cK[ks * 4 * C::LDK + ni * 8];
+                for (int ks = 0; ks < W_BK / 4; ++ks) {
+                    double a[8], b[4];
 #pragma unroll
-                        for (int mi = 0; mi < 8; ++mi) a[mi] = cW[mi * (WM * 8 * W_BK) + offA[ks]];
+                    for (int ni = 0; ni < 4; ++ni) b[ni] = cK[ks * 4 * C::LDK + ni * 8];
 #pragma unroll
-                        for (int mi = 0; mi < 8; ++mi)
+                    for (int mi = 0; mi < 8; ++mi) a[mi] = cW[mi * (WM * 8 * W_BK) + offA[ks]];
+#pragma unroll
+                    for (int mi = 0; mi < 8; ++mi)
+#pragma unroll
+                        for (int ni = 0; ni < 4; ++ni)
+                            dmma884(acc[mi][ni][0], acc[mi][ni][1], a[mi], b[ni]);
+                }
+            } else {
+                gen_math(v);
+                // diagonal / ragged block: fragment f = wm + WM*mi is needed for
+                // k-steps starting below 8*(f+1)
+                const int kl = c * W_BK - kd0;
+#pragma unroll
+                for (int ks = 0; ks < W_BK / 4; ++ks) {
+                    const int fmin = (kl + ks * 4) >> 3;                 // may be negative
+                    int mi0 = (fmin - wm + WM - 1) / WM;
+                    mi0 = (fmin - wm) <= 0 ? 0 : mi0;
+                    if (mi0 >= mi_lim) continue;
+                    double b[4];
+#pragma unroll
+                    for (int ni = 0; ni < 4; ++ni) b[ni] = cK[ks * 4 * C::LDK + ni * 8];
+#pragma unroll
+                    for (int mi = 0; mi < 8; ++mi) {
+                        if (mi >= mi0 && mi < mi_lim) {
+                            const double a = cW[mi * (WM * 8 * W_BK) + offA[ks]];
 #pragma unroll
                             for (int ni = 0; ni < 4; ++ni)
-                                dmma884(acc[mi][ni][0], acc[mi][ni][1], a[mi], b[ni]);
-                    }
-                } else {
-                    // diagonal / ragged block: fragment f = wm + WM*mi is needed for
-                    // k-steps starting below 8*(f+1)
-                    const int kl = c * W_BK - kd0;
-#pragma unroll
-                    for (int ks = 0; ks < W_BK / 4; ++ks) {
-                        const int fmin = (kl + ks * 4) >> 3;                 // may be negative
-                        int mi0 = (fmin - wm + WM - 1) / WM;
-                        mi0 = (fmin - wm) <= 0 ? 0 : mi0;
-                        if (mi0 >= mi_lim) continue;
-                        double b[4];
-#pragma unroll
-                        for (int ni = 0; ni < 4; ++ni) b[ni] = cK[ks * 4 * C::LDK + ni * 8];
-#pragma unroll
-                        for (int mi = 0; mi < 8; ++mi) {
-                            if (mi >= mi0 && mi < mi_lim) {
-                                const double a = cW[mi * (WM * 8 * W_BK) + offA[ks]];
-#pragma unroll
-                                for (int ni = 0; ni < 4; ++ni)
-                                    dmma884(acc[mi][ni][0], acc[mi][ni][1], a, b[ni]);
-                            }
+                                dmma884(acc[mi][ni][0], acc[mi][ni][1], a, b[ni]);
                         }
                     }
                 }
-                __syncwarp();
-                if (lane == 0) mbar_arrive(bar_empty + 8 * st);
             }
-            // column sums of squares of this row block's V fragments
+            __syncwarp();
+            if (lane == 0) mbar_arrive(bar_empty + 8 * st);
+            if (has_g) gen_end(v, al);
+
+            if (c == cit.nsl - 1) {
+                // end of a row block: column sums of squares of its V fragments
 #pragma unroll
-            for (int ni = 0; ni < 4; ++ni) {
-                double p0 = 0.0, p1 = 0.0;
+                for (int ni = 0; ni < 4; ++ni) {
+                    double p0 = 0.0, p1 = 0.0;
 #pragma unroll
-                for (int mi = 0; mi < 8; ++mi) {
-                    p0 = fma(acc[mi][ni][0], acc[mi][ni][0], p0);
-                    p1 = fma(acc[mi][ni][1], acc[mi][ni][1], p1);
-                }
+                    for (int mi = 0; mi < 8; ++mi) {
+                        p0 = fma(acc[mi][ni][0], acc[mi][ni][0], p0);
+                        p1 = fma(acc[mi][ni][1], acc[mi][ni][1], p1);
+                        acc[mi][ni][0] = acc[mi][ni][1] = 0.0;
+                    }
 #pragma unroll
-                for (int o = 4; o < 32; o <<= 1) {
-                    p0 += __shfl_xor_sync(0xffffffffu, p0, o);
-                    p1 += __shfl_xor_sync(0xffffffffu, p1, o);
+                    for (int o = 4; o < 32; o <<= 1) {
+                        p0 += __shfl_xor_sync(0xffffffffu, p0, o);
+                        p1 += __shfl_xor_sync(0xffffffffu, p1, o);
+                    }
+                    if (lr == 0) {
+                        wpart[wm * C::MT + wn * 32 + ni * 8 + lc * 2] = p0;
+                        wpart[wm * C::MT + wn * 32 + ni * 8 + lc * 2 + 1] = p1;
+                    }
                 }
-                if (lr == 0) {
-                    wpart[wm * C::MT + wn * 32 + ni * 8 + lc * 2] = p0;
-                    wpart[wm * C::MT + wn * 32 + ni * 8 + lc * 2 + 1] = p1;
+                math_bar_sync();
+                if (t < C::MT) {
+                    double a2 = colsum[t];
+#pragma unroll
+                    for (int w = 0; w < WM; ++w) a2 += wpart[w * C::MT + t];
+                    colsum[t] = a2;
                 }
+                math_bar_sync();
             }
-            consumer_bar_sync();
-            if (t < C::MT) {
-                double a2 = colsum[t];
-#pragma unroll
-                for (int w = 0; w < WM; ++w) a2 += wpart[w * C::MT + t];
-                colsum[t] = a2;
-            }
-            consumer_bar_sync();
+            advance(cit);
         }
+        cp_async_wait<0>();
+        smean[t] = macc;
     }
     __syncthreads();
     if (t < C::MT) {
@@ -402,7 +451,7 @@ predict_ws_kernel(const __grid_constant__ CUtensorMap tmW, gpx_kernel_params kp,
             if (mu) {
                 const double m0 = m_new ? m_new[(size_t)s * M + gj] : m_const;
                 double dot = 0.0;
-                for (int q = t; q < W_PROD_THREADS; q += C::MT) dot += smean[q];
+                for (int q = t; q < W_MATH_THREADS; q += C::MT) dot += smean[q];
                 mu[(size_t)s * M + gj] = m0 + dot;
             }
         }
