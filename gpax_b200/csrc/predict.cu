@@ -127,6 +127,55 @@ predict_prep_kernel(gpx_kernel_params kp, int n, const double *__restrict__ x,
 // ---------------------------------------------------------------------------
 // main kernel
 // ---------------------------------------------------------------------------
+// Half a slice (two k-steps KS0, KS0+1) of DMMAs for the fragments mi >= MI0 of
+// this warp, with the generator steps [SLO, SHI) spread evenly between them.
+// MI0 is a template parameter so that fragments above the diagonal are skipped
+// by a real branch in the caller (ptxas turns per-fragment `if`s into predicated
+// DMMAs, and a predicated-off DMMA still occupies the pipe for its 16 cycles).
+template <int MI0, int KS0, int SLO, int SHI, int WM, int LDK, class Gen>
+__device__ __forceinline__ void mma_half(double (&acc)[8][4][2], const double *cW, const double *cK,
+                                         const int (&offA)[W_BK / 4], Gen &gen, double scale) {
+    constexpr int NF = 8 - MI0, ND = 2 * NF * 4, NS = SHI - SLO;
+    if (ND == 0) {
+        gen.run(SLO, SHI, scale);
+        return;
+    }
+#pragma unroll
+    for (int kk = 0; kk < 2; ++kk) {
+        const int ks = KS0 + kk;
+        double b[4];
+#pragma unroll
+        for (int ni = 0; ni < 4; ++ni) b[ni] = cK[ks * 4 * LDK + ni * 8];
+#pragma unroll
+        for (int mi = MI0; mi < 8; ++mi) {
+            const double a = cW[mi * (WM * 8 * W_BK) + offA[ks]];
+#pragma unroll
+            for (int ni = 0; ni < 4; ++ni) {
+                dmma884(acc[mi][ni][0], acc[mi][ni][1], a, b[ni]);
+                const int j = (kk * NF + (mi - MI0)) * 4 + ni;
+                gen.run(SLO + (j * NS) / ND, SLO + ((j + 1) * NS) / ND, scale);
+            }
+        }
+    }
+}
+
+template <int KS0, int SLO, int SHI, int WM, int LDK, class Gen>
+__device__ __forceinline__ void mma_half_from(int mi0, double (&acc)[8][4][2], const double *cW,
+                                              const double *cK, const int (&offA)[W_BK / 4],
+                                              Gen &gen, double scale) {
+    switch (mi0) {
+        case 0: mma_half<0, KS0, SLO, SHI, WM, LDK>(acc, cW, cK, offA, gen, scale); break;
+        case 1: mma_half<1, KS0, SLO, SHI, WM, LDK>(acc, cW, cK, offA, gen, scale); break;
+        case 2: mma_half<2, KS0, SLO, SHI, WM, LDK>(acc, cW, cK, offA, gen, scale); break;
+        case 3: mma_half<3, KS0, SLO, SHI, WM, LDK>(acc, cW, cK, offA, gen, scale); break;
+        case 4: mma_half<4, KS0, SLO, SHI, WM, LDK>(acc, cW, cK, offA, gen, scale); break;
+        case 5: mma_half<5, KS0, SLO, SHI, WM, LDK>(acc, cW, cK, offA, gen, scale); break;
+        case 6: mma_half<6, KS0, SLO, SHI, WM, LDK>(acc, cW, cK, offA, gen, scale); break;
+        case 7: mma_half<7, KS0, SLO, SHI, WM, LDK>(acc, cW, cK, offA, gen, scale); break;
+        default: mma_half<8, KS0, SLO, SHI, WM, LDK>(acc, cW, cK, offA, gen, scale); break;
+    }
+}
+
 struct SliceIter {
     int rb, c, nsl;
 };
@@ -142,8 +191,8 @@ predict_ws_kernel(const __grid_constant__ CUtensorMap tmW, gpx_kernel_params kp,
     extern __shared__ unsigned char smem_raw[];
     // 1024-byte alignment: the 128-byte TMA swizzle pattern is a function of the
     // shared-memory address bits [4:9]
-    double *sW = reinterpret_cast<double *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
-                                            ~(uintptr_t)1023);
+    // (offset arithmetic on the array itself keeps the shared address space -> LDS, not LD)
+    double *sW = reinterpret_cast<double *>(smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u));
     double *sK = sW + (size_t)C::NST * C::W_STAGE;        // [NST][W_BK][LDK]
     double *sZ = sK + (size_t)C::NST * C::K_STAGE;        // [MT][MAX_D+1]
     double *colsum = sZ + C::MT * (GPX_MAX_D + 1);        // [MT]
@@ -245,8 +294,11 @@ predict_ws_kernel(const __grid_constant__ CUtensorMap tmW, gpx_kernel_params kp,
         SliceIter git{0, 0, nsl_of(0)};
         double macc = 0.0;
         prefetch_rows(0, 0);
+        constexpr int GKIND = KIND;     // PERIODIC runs the RBF-shaped exp with factor -2
+        using Gen = KGen<GKIND, GEN>;
+        constexpr int NS = Gen::NSTEPS;
         // gen_begin: distances of this thread's GEN entries of slice gi (registers only)
-        auto gen_begin = [&](double (&v)[GEN], double (&al)[GEN]) {
+        auto gen_begin = [&](Gen &g, double (&al)[GEN]) {
             const int buf = gi & 1;
             __syncwarp();                             // everyone is done with buf ^ 1
             SliceIter nx = git;
@@ -265,53 +317,36 @@ predict_ws_kernel(const __grid_constant__ CUtensorMap tmW, gpx_kernel_params kp,
                         double sn = sin(GPX_PI * df / s_per[q]) / s_len[q];
                         acc += sn * sn;
                     }
-                    v[i] = acc;                        // exponent / -2
+                    g.v[i] = acc;
                 } else {
                     double xz = 0.0;
                     for (int q = 0; q < d; ++q) xz = fma(pz[q], px[q], xz);
-                    v[i] = fmax((z2n - 2.0 * xz) + px[d], 0.0);
+                    g.v[i] = fmax((z2n - 2.0 * xz) + px[d], 0.0);
                 }
                 al[i] = px[d + 1];
             }
         };
-        // gen_math: straight-line N-wide exp / sqrt (common.cuh) so that the compiler
-        // can interleave it with the DMMA stream of the same warp
-        auto gen_math = [&](double (&v)[GEN]) {
-            constexpr int GB = GEN < 4 ? GEN : 4;
-#pragma unroll
-            for (int g = 0; g < GEN / GB; ++g) {
-                double w[GB];
-#pragma unroll
-                for (int i = 0; i < GB; ++i) w[i] = v[g * GB + i];
-                if (KIND == GPX_PERIODIC) {
-#pragma unroll
-                    for (int i = 0; i < GB; ++i) w[i] = 4.0 * w[i];   // exp(-2a) = rbf form exp(-0.5 * 4a)
-                    k_from_r2_vec<GPX_RBF, GB>(w, scale);
-                } else {
-                    k_from_r2_vec<KIND == GPX_PERIODIC ? GPX_RBF : KIND, GB>(w, scale);
-                }
-#pragma unroll
-                for (int i = 0; i < GB; ++i) v[g * GB + i] = w[i];
-            }
-        };
-        // gen_end: publish the entries into the stage of slice gi
-        auto gen_end = [&](double (&v)[GEN], double (&al)[GEN]) {
+        // tma_issue (one elected thread): as soon as the stage of slice gi is released,
+        // stream the W slab of that slice into it -- two slices ahead of its use
+        auto tma_issue = [&]() {
             const uint32_t gst = gi % C::NST, gph = (gi / C::NST) & 1;
             mbar_wait(bar_empty + 8 * gst, gph ^ 1);
-            if (t == 0) {
-                // the stage is free: stream the W slab of slice gi into it (TMA)
-                mbar_arrive_expect_tx(bar_fullW + 8 * gst, (uint32_t)(C::W_STAGE * sizeof(double)));
+            mbar_arrive_expect_tx(bar_fullW + 8 * gst, (uint32_t)(C::W_STAGE * sizeof(double)));
 #pragma unroll
-                for (int b = 0; b < C::NBOX; ++b)
-                    tma_load_3d(smem_u32(sW + (size_t)gst * C::W_STAGE + b * C::BOX_ROWS * W_BK), &tmW,
-                                bar_fullW + 8 * gst, git.c * W_BK, git.rb * C::R + b * C::BOX_ROWS, s);
-            }
+            for (int b = 0; b < C::NBOX; ++b)
+                tma_load_3d(smem_u32(sW + (size_t)gst * C::W_STAGE + b * C::BOX_ROWS * W_BK), &tmW,
+                            bar_fullW + 8 * gst, git.c * W_BK, git.rb * C::R + b * C::BOX_ROWS, s);
+        };
+        // gen_end: publish the entries into the stage of slice gi
+        auto gen_end = [&](Gen &g, double (&al)[GEN]) {
+            const uint32_t gst = gi % C::NST, gph = (gi / C::NST) & 1;
+            mbar_wait(bar_empty + 8 * gst, gph ^ 1);
             double *dst = sK + (size_t)gst * C::K_STAGE + g_j;
             const bool do_mean = (git.rb == NRB - 1);
 #pragma unroll
             for (int i = 0; i < GEN; ++i) {
                 const int kk = g_k0 + i * KSTEP;
-                const double vv = (git.c * W_BK + kk < n) ? v[i] : 0.0;
+                const double vv = (git.c * W_BK + kk < n) ? g.v[i] : 0.0;
                 dst[kk * C::LDK] = vv;
                 if (do_mean) macc = fma(vv, al[i], macc);
             }
@@ -322,10 +357,12 @@ predict_ws_kernel(const __grid_constant__ CUtensorMap tmW, gpx_kernel_params kp,
         };
         // prologue: the first D slices
         for (int q = 0; q < D && gi < T; ++q) {
-            double v[GEN], al[GEN];
-            gen_begin(v, al);
-            gen_math(v);
-            gen_end(v, al);
+            Gen g;
+            double al[GEN];
+            if (t == 0) tma_issue();
+            gen_begin(g, al);
+            g.run(0, NS, scale);
+            gen_end(g, al);
         }
 
         // swizzled A-fragment offsets: row = 8 f + lr, 16-byte chunk (2 ks + lc/2) ^ lr
@@ -351,35 +388,35 @@ predict_ws_kernel(const __grid_constant__ CUtensorMap tmW, gpx_kernel_params kp,
             const int c = cit.c;
 
             const bool has_g = gi < T;
-            double v[GEN], al[GEN];
+            Gen g;
+            double al[GEN];
 #pragma unroll
-            for (int q = 0; q < GEN; ++q) v[q] = 0.0, al[q] = 0.0;
-            if (has_g) gen_begin(v, al);
+            for (int q = 0; q < GEN; ++q) g.v[q] = 0.0, al[q] = 0.0;
+            if (has_g) {
+                if (t == 0) tma_issue();
+                gen_begin(g, al);
+            }
 
             const uint32_t st = i % C::NST, ph = (i / C::NST) & 1;
             mbar_wait(bar_fullW + 8 * st, ph);
             mbar_wait(bar_fullK + 8 * st, ph);
             const double *cW = sW + (size_t)st * C::W_STAGE;
             const double *cK = sK + (size_t)st * C::K_STAGE + offB;
-            if (c < nsl_full && mi_lim >= 8) {
-                gen_math(v);        // same basic block as the DMMAs below: interleaved by ptxas
-#pragma unroll
-                for (int ks = 0; ks < W_BK / 4; ++ks) {
-                    double a[8], b[4];
-#pragma unroll
-                    for (int ni = 0; ni < 4; ++ni) b[ni] = cK[ks * 4 * C::LDK + ni * 8];
-#pragma unroll
-                    for (int mi = 0; mi < 8; ++mi) a[mi] = cW[mi * (WM * 8 * W_BK) + offA[ks]];
-#pragma unroll
-                    for (int mi = 0; mi < 8; ++mi)
-#pragma unroll
-                        for (int ni = 0; ni < 4; ++ni)
-                            dmma884(acc[mi][ni][0], acc[mi][ni][1], a[mi], b[ni]);
+            if (mi_lim >= 8) {
+                // fragment f = wm + WM*mi is needed for k-steps starting below 8*(f+1):
+                // first fragment index per half slice (0 below the diagonal block)
+                const int kl = c * W_BK - kd0;
+                int mi0a = 0, mi0b = 0;
+                if (kl >= 0) {
+                    const int fa = kl >> 3, fb = fa + 1;
+                    mi0a = fa <= wm ? 0 : (fa - wm + WM - 1) / WM;
+                    mi0b = fb <= wm ? 0 : (fb - wm + WM - 1) / WM;
                 }
+                mma_half_from<0, 0, NS / 2, WM, C::LDK>(mi0a, acc, cW, cK, offA, g, scale);
+                mma_half_from<2, NS / 2, NS, WM, C::LDK>(mi0b, acc, cW, cK, offA, g, scale);
             } else {
-                gen_math(v);
-                // diagonal / ragged block: fragment f = wm + WM*mi is needed for
-                // k-steps starting below 8*(f+1)
+                g.run(0, NS, scale);
+                // ragged last row block (n not a multiple of R): predicated fragments
                 const int kl = c * W_BK - kd0;
 #pragma unroll
                 for (int ks = 0; ks < W_BK / 4; ++ks) {
@@ -403,7 +440,7 @@ predict_ws_kernel(const __grid_constant__ CUtensorMap tmW, gpx_kernel_params kp,
             }
             __syncwarp();
             if (lane == 0) mbar_arrive(bar_empty + 8 * st);
-            if (has_g) gen_end(v, al);
+            if (has_g) gen_end(g, al);
 
             if (c == cit.nsl - 1) {
                 // end of a row block: column sums of squares of its V fragments
