@@ -36,32 +36,30 @@
 
 namespace gpx {
 
-constexpr int W_MATH_WARPS = 8;                                 // K* generation + DMMA
-constexpr int W_MATH_THREADS = W_MATH_WARPS * 32;               // 256
-constexpr int W_THREADS = W_MATH_THREADS;                       // 256 (up to 255 regs/thread)
-constexpr int W_BK = 16;                                        // 128-byte rows = one swizzle span
-constexpr int W_GEN_AHEAD = 2;                                  // K* slices are generated this many slices ahead
-constexpr int W_XS = GPX_MAX_D + 2;                             // staged training row: coords, norm, alpha
+constexpr int W_WARPS = 16;                    // every warp generates K* entries and issues DMMAs
+constexpr int W_THREADS = W_WARPS * 32;        // 512 (128 registers per thread)
+constexpr int W_BK = 16;                       // 128-byte rows = one swizzle span
+constexpr int W_GEN_AHEAD = 2;                 // K* slices are generated this many slices ahead
+constexpr int W_MF = 4, W_NF = 4;              // per-warp fragment grid: 32 rows x 32 candidates
 
-template <int WM, int WN>
+template <int WN>
 struct WCfg {
-    static_assert(WM * WN == W_MATH_WARPS, "8 math warps");
-    static constexpr int R = WM * 64;          // W rows per pass
-    static constexpr int MT = WN * 32;         // candidates per CTA
+    static constexpr int WM = W_WARPS / WN;    // warps along the rows; fragment f = wm + WM * mi
+    static constexpr int R = WM * W_MF * 8;    // W rows per pass (512 for WN = 1, 256 for WN = 2)
+    static constexpr int MT = WN * W_NF * 8;   // candidates per CTA (32 / 64)
     static constexpr int NST = (R >= 512) ? 3 : 4;
     static constexpr int LDK = MT + 4;         // K*^T slice, k-major [W_BK][LDK]
     static constexpr int W_STAGE = R * W_BK;   // doubles (R * 128 bytes, multiple of 1024)
     static constexpr int K_STAGE = W_BK * LDK;
     static constexpr int BOX_ROWS = (R > 256) ? 256 : R;
     static constexpr int NBOX = R / BOX_ROWS;
-    static constexpr int KSTEP = W_MATH_THREADS / MT;   // k rows generated per pass over the slice
-    static constexpr int GEN = W_BK / KSTEP;            // K* entries per thread per slice
+    static constexpr int KSTEP = W_THREADS / MT;        // k rows generated per pass over the slice
+    static constexpr int GEN = W_BK / KSTEP;            // K* entries per thread per slice (1 / 2)
     static_assert(KSTEP >= 1 && KSTEP * GEN == W_BK, "generator mapping");
     static constexpr size_t SMEM_BYTES =
         1024 /*alignment slack*/ +
         sizeof(double) * ((size_t)NST * W_STAGE + (size_t)NST * K_STAGE + MT * (GPX_MAX_D + 1) +
-                          MT /*colsum*/ + WM * MT /*wpart*/ + W_MATH_THREADS /*smean*/ +
-                          2 * GPX_MAX_D + W_MATH_WARPS * 2 * GEN * W_XS /*sXW*/) +
+                          MT /*colsum*/ + WM * MT /*wpart*/ + W_THREADS /*smean*/ + 2 * GPX_MAX_D) +
         sizeof(uint64_t) * 3 * NST;
 };
 
@@ -96,23 +94,23 @@ __device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap *tm,
         "[%0], [%1, {%3, %4, %5}], [%2];\n" ::"r"(dst), "l"(tm), "r"(bar), "r"(c0), "r"(c1), "r"(c2)
         : "memory");
 }
-__device__ __forceinline__ void math_bar_sync() {
-    asm volatile("bar.sync 1, %0;\n" ::"n"(W_MATH_THREADS) : "memory");
-}
-
 // ---------------------------------------------------------------------------
 // prep: xs[s][k][0..d-1] = x_k / length_s (raw x for PERIODIC), [d] = squared
-// norm of the scaled point, [d+1] = alpha_s[k]
+// norm of the scaled point, [d+1] = alpha_s[k]; k < n_pad = n rounded up to W_BK
 // ---------------------------------------------------------------------------
 template <int KIND>
 __global__ void __launch_bounds__(256)
-predict_prep_kernel(gpx_kernel_params kp, int n, const double *__restrict__ x,
+predict_prep_kernel(gpx_kernel_params kp, int n, int n_pad, const double *__restrict__ x,
                     const double *__restrict__ alpha, double *__restrict__ xs) {
     const int64_t s = blockIdx.y;
     const int k = blockIdx.x * 256 + threadIdx.x;
-    if (k >= n) return;
+    if (k >= n_pad) return;
     const int d = kp.d, XS = d + 2;
-    double *dst = xs + ((size_t)s * n + k) * XS;
+    double *dst = xs + ((size_t)s * n_pad + k) * XS;
+    if (k >= n) {            // padding rows: finite values, alpha = 0 (W columns >= n read as 0)
+        for (int q = 0; q < XS; ++q) dst[q] = 0.0;
+        return;
+    }
     double nrm = 0.0;
     for (int q = 0; q < d; ++q) {
         double v = x[(size_t)k * d + q];
@@ -124,18 +122,17 @@ predict_prep_kernel(gpx_kernel_params kp, int n, const double *__restrict__ x,
     dst[d + 1] = alpha[(size_t)s * n + k];
 }
 
-// ---------------------------------------------------------------------------
-// main kernel
-// ---------------------------------------------------------------------------
 // Half a slice (two k-steps KS0, KS0+1) of DMMAs for the fragments mi >= MI0 of
-// this warp, with the generator steps [SLO, SHI) spread evenly between them.
+// this warp, with the generator steps [SLO, SHI) spread evenly between them (the
+// DMMA that follows a step hides the latency of the step's result).
 // MI0 is a template parameter so that fragments above the diagonal are skipped
 // by a real branch in the caller (ptxas turns per-fragment `if`s into predicated
 // DMMAs, and a predicated-off DMMA still occupies the pipe for its 16 cycles).
 template <int MI0, int KS0, int SLO, int SHI, int WM, int LDK, class Gen>
-__device__ __forceinline__ void mma_half(double (&acc)[8][4][2], const double *cW, const double *cK,
-                                         const int (&offA)[W_BK / 4], Gen &gen, double scale) {
-    constexpr int NF = 8 - MI0, ND = 2 * NF * 4, NS = SHI - SLO;
+__device__ __forceinline__ void mma_half(double (&acc)[W_MF][W_NF][2], const double *cW,
+                                         const double *cK, const int (&offA)[W_BK / 4], Gen &gen,
+                                         double scale) {
+    constexpr int NFR = W_MF - MI0, ND = 2 * NFR * W_NF, NS = SHI - SLO;
     if (ND == 0) {
         gen.run(SLO, SHI, scale);
         return;
@@ -143,16 +140,16 @@ __device__ __forceinline__ void mma_half(double (&acc)[8][4][2], const double *c
 #pragma unroll
     for (int kk = 0; kk < 2; ++kk) {
         const int ks = KS0 + kk;
-        double b[4];
+        double b[W_NF];
 #pragma unroll
-        for (int ni = 0; ni < 4; ++ni) b[ni] = cK[ks * 4 * LDK + ni * 8];
+        for (int ni = 0; ni < W_NF; ++ni) b[ni] = cK[ks * 4 * LDK + ni * 8];
 #pragma unroll
-        for (int mi = MI0; mi < 8; ++mi) {
+        for (int mi = MI0; mi < W_MF; ++mi) {
             const double a = cW[mi * (WM * 8 * W_BK) + offA[ks]];
 #pragma unroll
-            for (int ni = 0; ni < 4; ++ni) {
+            for (int ni = 0; ni < W_NF; ++ni) {
                 dmma884(acc[mi][ni][0], acc[mi][ni][1], a, b[ni]);
-                const int j = (kk * NF + (mi - MI0)) * 4 + ni;
+                const int j = (kk * NFR + (mi - MI0)) * W_NF + ni;
                 gen.run(SLO + (j * NS) / ND, SLO + ((j + 1) * NS) / ND, scale);
             }
         }
@@ -160,34 +157,30 @@ __device__ __forceinline__ void mma_half(double (&acc)[8][4][2], const double *c
 }
 
 template <int KS0, int SLO, int SHI, int WM, int LDK, class Gen>
-__device__ __forceinline__ void mma_half_from(int mi0, double (&acc)[8][4][2], const double *cW,
-                                              const double *cK, const int (&offA)[W_BK / 4],
-                                              Gen &gen, double scale) {
+__device__ __forceinline__ void mma_half_from(int mi0, double (&acc)[W_MF][W_NF][2],
+                                              const double *cW, const double *cK,
+                                              const int (&offA)[W_BK / 4], Gen &gen, double scale) {
     switch (mi0) {
         case 0: mma_half<0, KS0, SLO, SHI, WM, LDK>(acc, cW, cK, offA, gen, scale); break;
         case 1: mma_half<1, KS0, SLO, SHI, WM, LDK>(acc, cW, cK, offA, gen, scale); break;
         case 2: mma_half<2, KS0, SLO, SHI, WM, LDK>(acc, cW, cK, offA, gen, scale); break;
         case 3: mma_half<3, KS0, SLO, SHI, WM, LDK>(acc, cW, cK, offA, gen, scale); break;
-        case 4: mma_half<4, KS0, SLO, SHI, WM, LDK>(acc, cW, cK, offA, gen, scale); break;
-        case 5: mma_half<5, KS0, SLO, SHI, WM, LDK>(acc, cW, cK, offA, gen, scale); break;
-        case 6: mma_half<6, KS0, SLO, SHI, WM, LDK>(acc, cW, cK, offA, gen, scale); break;
-        case 7: mma_half<7, KS0, SLO, SHI, WM, LDK>(acc, cW, cK, offA, gen, scale); break;
-        default: mma_half<8, KS0, SLO, SHI, WM, LDK>(acc, cW, cK, offA, gen, scale); break;
+        default: mma_half<4, KS0, SLO, SHI, WM, LDK>(acc, cW, cK, offA, gen, scale); break;
     }
 }
 
-struct SliceIter {
-    int rb, c, nsl;
-};
-
-template <int KIND, int WM, int WN>
+// ---------------------------------------------------------------------------
+// main kernel
+// ---------------------------------------------------------------------------
+template <int KIND, int WN>
 __global__ void __launch_bounds__(W_THREADS, 1)
-predict_ws_kernel(const __grid_constant__ CUtensorMap tmW, gpx_kernel_params kp, int n, int M,
-                  const double *__restrict__ xs, const double *__restrict__ xnew,
+predict_ws_kernel(const __grid_constant__ CUtensorMap tmW, gpx_kernel_params kp, int n, int n_pad,
+                  int M, const double *__restrict__ xs, const double *__restrict__ xnew,
                   const double *__restrict__ m_new, double m_const,
                   const double *__restrict__ diag_add, double *__restrict__ mu,
                   double *__restrict__ var) {
-    using C = WCfg<WM, WN>;
+    using C = WCfg<WN>;
+    constexpr int WM = C::WM, GEN = C::GEN, KSTEP = C::KSTEP, D = W_GEN_AHEAD;
     extern __shared__ unsigned char smem_raw[];
     // 1024-byte alignment: the 128-byte TMA swizzle pattern is a function of the
     // shared-memory address bits [4:9]
@@ -197,11 +190,10 @@ predict_ws_kernel(const __grid_constant__ CUtensorMap tmW, gpx_kernel_params kp,
     double *sZ = sK + (size_t)C::NST * C::K_STAGE;        // [MT][MAX_D+1]
     double *colsum = sZ + C::MT * (GPX_MAX_D + 1);        // [MT]
     double *wpart = colsum + C::MT;                       // [WM][MT]
-    double *smean = wpart + WM * C::MT;                   // [W_MATH_THREADS]
-    double *s_len = smean + W_MATH_THREADS;               // [MAX_D]
+    double *smean = wpart + WM * C::MT;                   // [W_THREADS]
+    double *s_len = smean + W_THREADS;                    // [MAX_D]
     double *s_per = s_len + GPX_MAX_D;                    // [MAX_D]
-    double *sXW = s_per + GPX_MAX_D;                      // [W_MATH_WARPS][2][GEN][W_XS]
-    uint64_t *bars = reinterpret_cast<uint64_t *>(sXW + W_MATH_WARPS * 2 * C::GEN * W_XS);
+    uint64_t *bars = reinterpret_cast<uint64_t *>(s_per + GPX_MAX_D);
 
     const int s = blockIdx.y;
     const int j0 = blockIdx.x * C::MT;
@@ -219,9 +211,9 @@ predict_ws_kernel(const __grid_constant__ CUtensorMap tmW, gpx_kernel_params kp,
     if (t == 0) {
 #pragma unroll
         for (int i = 0; i < C::NST; ++i) {
-            mbar_init(bar_fullW + 8 * i, 1);               // the expect_tx arrive of the TMA thread
-            mbar_init(bar_fullK + 8 * i, W_MATH_WARPS);    // one elected lane per math warp
-            mbar_init(bar_empty + 8 * i, W_MATH_WARPS);
+            mbar_init(bar_fullW + 8 * i, 1);           // the expect_tx arrive of the TMA thread
+            mbar_init(bar_fullK + 8 * i, W_WARPS);     // one elected lane per warp
+            mbar_init(bar_empty + 8 * i, W_WARPS);
         }
         asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
         asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory");
@@ -247,146 +239,114 @@ predict_ws_kernel(const __grid_constant__ CUtensorMap tmW, gpx_kernel_params kp,
         const int kend = (n < (rb + 1) * C::R) ? n : (rb + 1) * C::R;
         return (kend + W_BK - 1) / W_BK;
     };
-    auto advance = [&](SliceIter &it) {
-        if (++it.c == it.nsl) {
-            ++it.rb;
-            it.c = 0;
-            it.nsl = it.rb < NRB ? nsl_of(it.rb) : 1;
-        }
-    };
     int T = 0;
     for (int rb = 0; rb < NRB; ++rb) T += nsl_of(rb);
 
-    {
-        // ===================== math warps: K* generation + DMMA =====================
-        constexpr int KSTEP = C::KSTEP, GEN = C::GEN, D = W_GEN_AHEAD;
-        const int wm = warp / WN, wn = warp % WN;
-        const int lr = lane >> 2, lc = lane & 3;
-        // ---- generator state: thread -> candidate g_j, k rows g_k0 + i*KSTEP ----
-        const int g_j = t % C::MT, g_k0 = t / C::MT;             // g_k0 is warp-uniform
-        const double *pz = sZ + g_j * (GPX_MAX_D + 1);
-        const int XS = d + 2;
-        const double *xs_s = xs + (size_t)s * n * XS;
-        const double z2n = pz[GPX_MAX_D];
-        // warp-private double buffer of the GEN staged training rows of a slice
-        // (scaled coordinates, norm, alpha), prefetched one slice ahead with cp.async
-        double *xw = sXW + warp * (2 * GEN * W_XS);
-        int cp_i[3], cp_col[3];
+    const int wm = warp / WN, wn = warp % WN;
+    const int lr = lane >> 2, lc = lane & 3;
+    // ---- generator: thread -> candidate g_j, k rows g_k0 + i*KSTEP (g_k0 is warp-uniform) ----
+    using Gen = KGen<KIND, GEN>;
+    constexpr int NS = Gen::NSTEPS;
+    const int g_j = t % C::MT, g_k0 = t / C::MT;
+    const double *pz = sZ + g_j * (GPX_MAX_D + 1);
+    const double z2n = pz[GPX_MAX_D];
+    const int XS = d + 2;
+    // lane q < XS holds entry q of the staged training row (coords, norm, alpha) of the
+    // slice being generated; it is fetched one slice ahead and broadcast with shuffles
+    const double *xrow = xs + ((size_t)s * n_pad + g_k0) * XS + (lane < XS ? lane : 0);
+    double xval[GEN];
+    int gi = 0, g_rb = 0, g_c = 0, g_nsl = nsl_of(0);     // next slice to generate
+    double macc = 0.0;
 #pragma unroll
-        for (int e = 0; e < 3; ++e) {
-            const int idx = lane + 32 * e;
-            cp_i[e] = idx < GEN * XS ? idx / XS : -1;
-            cp_col[e] = idx % XS;
-        }
-        auto prefetch_rows = [&](int c, int buf) {
+    for (int i = 0; i < GEN; ++i) xval[i] = __ldg(xrow + (size_t)(i * KSTEP) * XS);
+
+    // gen_begin: distances of this thread's GEN entries of slice gi (registers only)
+    auto gen_begin = [&](Gen &g, double (&al)[GEN]) {
 #pragma unroll
-            for (int e = 0; e < 3; ++e) {
-                if (cp_i[e] >= 0) {
-                    int gk = c * W_BK + g_k0 + cp_i[e] * KSTEP;
-                    gk = gk < n ? gk : n - 1;
-                    cp_async8(xw + (buf * GEN + cp_i[e]) * W_XS + cp_col[e],
-                              xs_s + (size_t)gk * XS + cp_col[e]);
+        for (int i = 0; i < GEN; ++i) {
+            if (KIND == GPX_PERIODIC) {
+                double acc = 0.0;
+                for (int q = 0; q < d; ++q) {
+                    double df = pz[q] - __shfl_sync(0xffffffffu, xval[i], q);
+                    double sn = sin(GPX_PI * df / s_per[q]) / s_len[q];
+                    acc += sn * sn;
                 }
+                g.v[i] = acc;
+            } else {
+                double xz = 0.0;
+                for (int q = 0; q < d; ++q) xz = fma(pz[q], __shfl_sync(0xffffffffu, xval[i], q), xz);
+                g.v[i] = fmax((z2n - 2.0 * xz) + __shfl_sync(0xffffffffu, xval[i], d), 0.0);
             }
-            cp_async_commit();
-        };
-        int gi = 0;                                   // next slice to generate
-        SliceIter git{0, 0, nsl_of(0)};
-        double macc = 0.0;
-        prefetch_rows(0, 0);
-        constexpr int GKIND = KIND;     // PERIODIC runs the RBF-shaped exp with factor -2
-        using Gen = KGen<GKIND, GEN>;
-        constexpr int NS = Gen::NSTEPS;
-        // gen_begin: distances of this thread's GEN entries of slice gi (registers only)
-        auto gen_begin = [&](Gen &g, double (&al)[GEN]) {
-            const int buf = gi & 1;
-            __syncwarp();                             // everyone is done with buf ^ 1
-            SliceIter nx = git;
-            advance(nx);
-            prefetch_rows(nx.rb < NRB ? nx.c : 0, buf ^ 1);
-            cp_async_wait<1>();
-            __syncwarp();                             // the warp's rows of slice gi landed
-            const double *rows = xw + buf * GEN * W_XS;
-#pragma unroll
-            for (int i = 0; i < GEN; ++i) {
-                const double *px = rows + i * W_XS;
-                if (KIND == GPX_PERIODIC) {
-                    double acc = 0.0;
-                    for (int q = 0; q < d; ++q) {
-                        double df = pz[q] - px[q];
-                        double sn = sin(GPX_PI * df / s_per[q]) / s_len[q];
-                        acc += sn * sn;
-                    }
-                    g.v[i] = acc;
-                } else {
-                    double xz = 0.0;
-                    for (int q = 0; q < d; ++q) xz = fma(pz[q], px[q], xz);
-                    g.v[i] = fmax((z2n - 2.0 * xz) + px[d], 0.0);
-                }
-                al[i] = px[d + 1];
-            }
-        };
-        // tma_issue (one elected thread): as soon as the stage of slice gi is released,
-        // stream the W slab of that slice into it -- two slices ahead of its use
-        auto tma_issue = [&]() {
-            const uint32_t gst = gi % C::NST, gph = (gi / C::NST) & 1;
-            mbar_wait(bar_empty + 8 * gst, gph ^ 1);
-            mbar_arrive_expect_tx(bar_fullW + 8 * gst, (uint32_t)(C::W_STAGE * sizeof(double)));
-#pragma unroll
-            for (int b = 0; b < C::NBOX; ++b)
-                tma_load_3d(smem_u32(sW + (size_t)gst * C::W_STAGE + b * C::BOX_ROWS * W_BK), &tmW,
-                            bar_fullW + 8 * gst, git.c * W_BK, git.rb * C::R + b * C::BOX_ROWS, s);
-        };
-        // gen_end: publish the entries into the stage of slice gi
-        auto gen_end = [&](Gen &g, double (&al)[GEN]) {
-            const uint32_t gst = gi % C::NST, gph = (gi / C::NST) & 1;
-            mbar_wait(bar_empty + 8 * gst, gph ^ 1);
-            double *dst = sK + (size_t)gst * C::K_STAGE + g_j;
-            const bool do_mean = (git.rb == NRB - 1);
-#pragma unroll
-            for (int i = 0; i < GEN; ++i) {
-                const int kk = g_k0 + i * KSTEP;
-                const double vv = (git.c * W_BK + kk < n) ? g.v[i] : 0.0;
-                dst[kk * C::LDK] = vv;
-                if (do_mean) macc = fma(vv, al[i], macc);
-            }
-            __syncwarp();
-            if (lane == 0) mbar_arrive(bar_fullK + 8 * gst);
-            ++gi;
-            advance(git);
-        };
-        // prologue: the first D slices
-        for (int q = 0; q < D && gi < T; ++q) {
-            Gen g;
-            double al[GEN];
-            if (t == 0) tma_issue();
-            gen_begin(g, al);
-            g.run(0, NS, scale);
-            gen_end(g, al);
+            al[i] = __shfl_sync(0xffffffffu, xval[i], d + 1);
         }
-
-        // swizzled A-fragment offsets: row = 8 f + lr, 16-byte chunk (2 ks + lc/2) ^ lr
-        int offA[W_BK / 4];
+        // fetch the rows of the next slice (first slice of the next row block after the last)
+        const int nc = (g_c + 1 < g_nsl) ? g_c + 1 : 0;
 #pragma unroll
-        for (int ks = 0; ks < W_BK / 4; ++ks)
-            offA[ks] = (wm * 8 + lr) * W_BK + ((((ks << 1) | (lc >> 1)) ^ lr) << 1) + (lc & 1);
-        const int offB = lc * C::LDK + wn * 32 + lr;
-
-        double acc[8][4][2];
+        for (int i = 0; i < GEN; ++i) xval[i] = __ldg(xrow + (size_t)(nc * W_BK + i * KSTEP) * XS);
+    };
+    // tma_issue (one elected thread): as soon as the stage of slice gi is released,
+    // stream the W slab of that slice into it -- two slices ahead of its use
+    auto tma_issue = [&]() {
+        const uint32_t gst = gi % C::NST, gph = (gi / C::NST) & 1;
+        mbar_wait(bar_empty + 8 * gst, gph ^ 1);
+        mbar_arrive_expect_tx(bar_fullW + 8 * gst, (uint32_t)(C::W_STAGE * sizeof(double)));
 #pragma unroll
-        for (int mi = 0; mi < 8; ++mi)
+        for (int b = 0; b < C::NBOX; ++b)
+            tma_load_3d(smem_u32(sW + (size_t)gst * C::W_STAGE + b * C::BOX_ROWS * W_BK), &tmW,
+                        bar_fullW + 8 * gst, g_c * W_BK, g_rb * C::R + b * C::BOX_ROWS, s);
+    };
+    // gen_end: publish the entries into the stage of slice gi
+    auto gen_end = [&](Gen &g, double (&al)[GEN]) {
+        const uint32_t gst = gi % C::NST, gph = (gi / C::NST) & 1;
+        mbar_wait(bar_empty + 8 * gst, gph ^ 1);
+        double *dst = sK + (size_t)gst * C::K_STAGE + g_k0 * C::LDK + g_j;
+        const bool do_mean = (g_rb == NRB - 1);
 #pragma unroll
-            for (int ni = 0; ni < 4; ++ni) acc[mi][ni][0] = acc[mi][ni][1] = 0.0;
-        SliceIter cit{0, 0, nsl_of(0)};
-        for (int i = 0; i < T; ++i) {
-            const int kd0 = cit.rb * C::R;
-            const int kend = (n < kd0 + C::R) ? n : kd0 + C::R;
-            const int nsl_full = kd0 / W_BK;
-            // fragments that hold rows < n in this block: f < fr_lim  <=>  mi < mi_lim
-            const int fr_lim = (kend - kd0 + 7) >> 3;
-            const int mi_lim = (fr_lim - wm + WM - 1) / WM;
-            const int c = cit.c;
+        for (int i = 0; i < GEN; ++i) {
+            dst[i * KSTEP * C::LDK] = g.v[i];
+            if (do_mean) macc = fma(g.v[i], al[i], macc);
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(bar_fullK + 8 * gst);
+        ++gi;
+        if (++g_c == g_nsl) {
+            g_c = 0;
+            ++g_rb;
+            g_nsl = g_rb < NRB ? nsl_of(g_rb) : 1;
+        }
+    };
+    // prologue: the first D slices
+    for (int q = 0; q < D && gi < T; ++q) {
+        Gen g;
+        double al[GEN];
+        if (t == 0) tma_issue();
+        gen_begin(g, al);
+        g.run(0, NS, scale);
+        gen_end(g, al);
+    }
 
+    // swizzled A-fragment offsets: row = 8 f + lr, 16-byte chunk (2 ks + lc/2) ^ lr
+    int offA[W_BK / 4];
+#pragma unroll
+    for (int ks = 0; ks < W_BK / 4; ++ks)
+        offA[ks] = (wm * 8 + lr) * W_BK + ((((ks << 1) | (lc >> 1)) ^ lr) << 1) + (lc & 1);
+    const int offB = lc * C::LDK + wn * 32 + lr;
+
+    double acc[W_MF][W_NF][2];
+#pragma unroll
+    for (int mi = 0; mi < W_MF; ++mi)
+#pragma unroll
+        for (int ni = 0; ni < W_NF; ++ni) acc[mi][ni][0] = acc[mi][ni][1] = 0.0;
+
+    uint32_t st = 0, ph = 0;          // stage / phase of the slice being multiplied
+    for (int rb = 0; rb < NRB; ++rb) {
+        const int kd0 = rb * C::R;
+        const int kend = (n < kd0 + C::R) ? n : kd0 + C::R;
+        const int nsl = (kend + W_BK - 1) / W_BK;
+        // fragments that hold rows < n in this block: f < fr_lim  <=>  mi < mi_lim
+        const int fr_lim = (kend - kd0 + 7) >> 3;
+        const int mi_lim = (fr_lim - wm + WM - 1) / WM;
+        for (int c = 0; c < nsl; ++c) {
             const bool has_g = gi < T;
             Gen g;
             double al[GEN];
@@ -396,16 +356,14 @@ predict_ws_kernel(const __grid_constant__ CUtensorMap tmW, gpx_kernel_params kp,
                 if (t == 0) tma_issue();
                 gen_begin(g, al);
             }
-
-            const uint32_t st = i % C::NST, ph = (i / C::NST) & 1;
             mbar_wait(bar_fullW + 8 * st, ph);
             mbar_wait(bar_fullK + 8 * st, ph);
             const double *cW = sW + (size_t)st * C::W_STAGE;
             const double *cK = sK + (size_t)st * C::K_STAGE + offB;
-            if (mi_lim >= 8) {
+            const int kl = c * W_BK - kd0;
+            if (mi_lim >= W_MF) {
                 // fragment f = wm + WM*mi is needed for k-steps starting below 8*(f+1):
                 // first fragment index per half slice (0 below the diagonal block)
-                const int kl = c * W_BK - kd0;
                 int mi0a = 0, mi0b = 0;
                 if (kl >= 0) {
                     const int fa = kl >> 3, fb = fa + 1;
@@ -417,22 +375,21 @@ predict_ws_kernel(const __grid_constant__ CUtensorMap tmW, gpx_kernel_params kp,
             } else {
                 g.run(0, NS, scale);
                 // ragged last row block (n not a multiple of R): predicated fragments
-                const int kl = c * W_BK - kd0;
 #pragma unroll
                 for (int ks = 0; ks < W_BK / 4; ++ks) {
                     const int fmin = (kl + ks * 4) >> 3;                 // may be negative
                     int mi0 = (fmin - wm + WM - 1) / WM;
                     mi0 = (fmin - wm) <= 0 ? 0 : mi0;
                     if (mi0 >= mi_lim) continue;
-                    double b[4];
+                    double b[W_NF];
 #pragma unroll
-                    for (int ni = 0; ni < 4; ++ni) b[ni] = cK[ks * 4 * C::LDK + ni * 8];
+                    for (int ni = 0; ni < W_NF; ++ni) b[ni] = cK[ks * 4 * C::LDK + ni * 8];
 #pragma unroll
-                    for (int mi = 0; mi < 8; ++mi) {
+                    for (int mi = 0; mi < W_MF; ++mi) {
                         if (mi >= mi0 && mi < mi_lim) {
                             const double a = cW[mi * (WM * 8 * W_BK) + offA[ks]];
 #pragma unroll
-                            for (int ni = 0; ni < 4; ++ni)
+                            for (int ni = 0; ni < W_NF; ++ni)
                                 dmma884(acc[mi][ni][0], acc[mi][ni][1], a, b[ni]);
                         }
                     }
@@ -440,43 +397,39 @@ predict_ws_kernel(const __grid_constant__ CUtensorMap tmW, gpx_kernel_params kp,
             }
             __syncwarp();
             if (lane == 0) mbar_arrive(bar_empty + 8 * st);
+            if (++st == C::NST) { st = 0; ph ^= 1; }
             if (has_g) gen_end(g, al);
-
-            if (c == cit.nsl - 1) {
-                // end of a row block: column sums of squares of its V fragments
-#pragma unroll
-                for (int ni = 0; ni < 4; ++ni) {
-                    double p0 = 0.0, p1 = 0.0;
-#pragma unroll
-                    for (int mi = 0; mi < 8; ++mi) {
-                        p0 = fma(acc[mi][ni][0], acc[mi][ni][0], p0);
-                        p1 = fma(acc[mi][ni][1], acc[mi][ni][1], p1);
-                        acc[mi][ni][0] = acc[mi][ni][1] = 0.0;
-                    }
-#pragma unroll
-                    for (int o = 4; o < 32; o <<= 1) {
-                        p0 += __shfl_xor_sync(0xffffffffu, p0, o);
-                        p1 += __shfl_xor_sync(0xffffffffu, p1, o);
-                    }
-                    if (lr == 0) {
-                        wpart[wm * C::MT + wn * 32 + ni * 8 + lc * 2] = p0;
-                        wpart[wm * C::MT + wn * 32 + ni * 8 + lc * 2 + 1] = p1;
-                    }
-                }
-                math_bar_sync();
-                if (t < C::MT) {
-                    double a2 = colsum[t];
-#pragma unroll
-                    for (int w = 0; w < WM; ++w) a2 += wpart[w * C::MT + t];
-                    colsum[t] = a2;
-                }
-                math_bar_sync();
-            }
-            advance(cit);
         }
-        cp_async_wait<0>();
-        smean[t] = macc;
+        // end of a row block: column sums of squares of its V fragments
+#pragma unroll
+        for (int ni = 0; ni < W_NF; ++ni) {
+            double p0 = 0.0, p1 = 0.0;
+#pragma unroll
+            for (int mi = 0; mi < W_MF; ++mi) {
+                p0 = fma(acc[mi][ni][0], acc[mi][ni][0], p0);
+                p1 = fma(acc[mi][ni][1], acc[mi][ni][1], p1);
+                acc[mi][ni][0] = acc[mi][ni][1] = 0.0;
+            }
+#pragma unroll
+            for (int o = 4; o < 32; o <<= 1) {
+                p0 += __shfl_xor_sync(0xffffffffu, p0, o);
+                p1 += __shfl_xor_sync(0xffffffffu, p1, o);
+            }
+            if (lr == 0) {
+                wpart[wm * C::MT + wn * 32 + ni * 8 + lc * 2] = p0;
+                wpart[wm * C::MT + wn * 32 + ni * 8 + lc * 2 + 1] = p1;
+            }
+        }
+        __syncthreads();
+        if (t < C::MT) {
+            double a2 = colsum[t];
+#pragma unroll
+            for (int w = 0; w < WM; ++w) a2 += wpart[w * C::MT + t];
+            colsum[t] = a2;
+        }
+        __syncthreads();
     }
+    smean[t] = macc;
     __syncthreads();
     if (t < C::MT) {
         const int gj = j0 + t;
@@ -488,7 +441,7 @@ predict_ws_kernel(const __grid_constant__ CUtensorMap tmW, gpx_kernel_params kp,
             if (mu) {
                 const double m0 = m_new ? m_new[(size_t)s * M + gj] : m_const;
                 double dot = 0.0;
-                for (int q = t; q < W_MATH_THREADS; q += C::MT) dot += smean[q];
+                for (int q = t; q < W_THREADS; q += C::MT) dot += smean[q];
                 mu[(size_t)s * M + gj] = m0 + dot;
             }
         }
@@ -532,15 +485,15 @@ static int make_w_tensormap(CUtensorMap *tm, const double *W, int64_t S, int64_t
     return 0;
 }
 
-template <int KIND, int WM, int WN>
+template <int KIND, int WN>
 static int launch_predict_ws(const gpx_kernel_params *kp, int64_t S, int64_t n, int64_t M,
                              const double *xs, const double *xnew, const double *W, int64_t ldw,
                              const double *m_new, double m_const, const double *diag_add,
                              double *mu, double *var, cudaStream_t st) {
-    using C = WCfg<WM, WN>;
+    using C = WCfg<WN>;
     static bool configured = false;
     if (!configured) {
-        cudaError_t e = cudaFuncSetAttribute(predict_ws_kernel<KIND, WM, WN>,
+        cudaError_t e = cudaFuncSetAttribute(predict_ws_kernel<KIND, WN>,
                                              cudaFuncAttributeMaxDynamicSharedMemorySize,
                                              (int)C::SMEM_BYTES);
         if (e != cudaSuccess) { set_error("gpx_predict: smem attribute failed (%d)", (int)e); return (int)e; }
@@ -550,8 +503,9 @@ static int launch_predict_ws(const gpx_kernel_params *kp, int64_t S, int64_t n, 
     int rc = make_w_tensormap(&tm, W, S, n, ldw, C::BOX_ROWS);
     if (rc) return rc;
     dim3 grid((unsigned)((M + C::MT - 1) / C::MT), (unsigned)S);
-    predict_ws_kernel<KIND, WM, WN><<<grid, W_THREADS, C::SMEM_BYTES, st>>>(
-        tm, *kp, (int)n, (int)M, xs, xnew, m_new, m_const, diag_add, mu, var);
+    const int n_pad = (int)((n + W_BK - 1) / W_BK * W_BK);
+    predict_ws_kernel<KIND, WN><<<grid, W_THREADS, C::SMEM_BYTES, st>>>(
+        tm, *kp, (int)n, n_pad, (int)M, xs, xnew, m_new, m_const, diag_add, mu, var);
     return 0;
 }
 
@@ -567,20 +521,22 @@ static int dispatch_predict(const gpx_kernel_params *kp, int64_t S, int64_t n, i
     if (n <= 128)
         return launch_predict<KIND, 2, 4, 16>(kp, S, n, M, x, xnew, W, ldw, alpha, m_new, m_const, diag_add, mu, var, st);
     if (!ws) { set_error("gpx_predict: workspace required for n > 128"); return -16; }
-    dim3 g((unsigned)((n + 255) / 256), (unsigned)S);
-    predict_prep_kernel<KIND><<<g, 256, 0, st>>>(*kp, (int)n, x, alpha, ws);
+    const int n_pad = (int)((n + W_BK - 1) / W_BK * W_BK);
+    dim3 g((unsigned)((n_pad + 255) / 256), (unsigned)S);
+    predict_prep_kernel<KIND><<<g, 256, 0, st>>>(*kp, (int)n, n_pad, x, alpha, ws);
     count_launches(1);
     // tall slabs amortise the K* regeneration for large n
     if (n <= 512)
-        return launch_predict_ws<KIND, 4, 2>(kp, S, n, M, ws, xnew, W, ldw, m_new, m_const, diag_add, mu, var, st);
-    return launch_predict_ws<KIND, 8, 1>(kp, S, n, M, ws, xnew, W, ldw, m_new, m_const, diag_add, mu, var, st);
+        return launch_predict_ws<KIND, 2>(kp, S, n, M, ws, xnew, W, ldw, m_new, m_const, diag_add, mu, var, st);
+    return launch_predict_ws<KIND, 1>(kp, S, n, M, ws, xnew, W, ldw, m_new, m_const, diag_add, mu, var, st);
 }
 
 }  // namespace gpx
 
 extern "C" size_t gpx_predict_ws_bytes(int64_t S, int64_t n, int32_t d) {
     if (n <= 128 || S <= 0) return 0;
-    return (size_t)S * (size_t)n * (size_t)(d + 2) * sizeof(double);
+    const size_t n_pad = (size_t)((n + gpx::W_BK - 1) / gpx::W_BK * gpx::W_BK);
+    return (size_t)S * n_pad * (size_t)(d + 2) * sizeof(double);
 }
 
 extern "C" int gpx_predict(const gpx_kernel_params *kp, int64_t S, int64_t n, int64_t M,
