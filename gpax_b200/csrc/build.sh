@@ -12,6 +12,7 @@ for f in api gram chol mll predict acq mll_grad; do
   extra=()
   # acquisition arithmetic must match NumPy's un-fused mul/add bit for bit
   [ "$f" = acq ] && extra=(-fmad=false)
+  [ "$f" = predict ] && [ -n "${GPX_PREDICT_DEBUG_VARIANTS:-}" ] && extra=(-DGPX_PREDICT_DEBUG_VARIANTS)
   ( "$NVCC" "${FLAGS[@]}" "${extra[@]}" -c "$here/$f.cu" -o "$here/obj/$f.o" > "$here/obj/$f.log" 2>&1 \
       || { cat "$here/obj/$f.log"; exit 1; } ) &
   pids+=($!)

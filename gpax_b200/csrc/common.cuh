@@ -7,6 +7,8 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <math.h>
+#include <utility>
+#include <type_traits>
 #include "../../include/gpax_b200.h"
 
 namespace gpx {
@@ -182,6 +184,16 @@ __device__ __forceinline__ void k_from_r2_vec(double (&v)[N], double scale) {
     }
 }
 
+// compile-time unrolled loop: f(std::integral_constant<int, 0>{}), ..., f(<N-1>)
+template <class F, int... Is>
+__device__ __forceinline__ void static_for_impl(F &&f, std::integer_sequence<int, Is...>) {
+    (f(std::integral_constant<int, Is>{}), ...);
+}
+template <int N, class F>
+__device__ __forceinline__ void static_for(F &&f) {
+    static_for_impl(static_cast<F &&>(f), std::make_integer_sequence<int, N>{});
+}
+
 // ---- step-wise generator -----------------------------------------------------
 // The same arithmetic as k_from_r2_vec cut into steps that are one FP64
 // instruction deep per entry, so that a caller can drop one step between its
@@ -195,63 +207,58 @@ struct KGen {
     double v[N], x[N], p[N], q[N], pl[N];
     int ni[N];
 
-    __device__ __forceinline__ void step(int st, double scale) {
+    template <int st>
+    __device__ __forceinline__ void step(double scale) {
         const double L2E = 1.4426950408889634, SHIFT = 6755399441055744.0;
         const double LN2_HI = 6.93147180369123816490e-01, LN2_LO = 1.90821492927058770002e-10;
-        const double c[14] = {1.0, 1.0, 0.5, 1.6666666666666666e-01, 4.1666666666666664e-02,
-                              8.3333333333333332e-03, 1.3888888888888889e-03, 1.9841269841269841e-04,
-                              2.4801587301587302e-05, 2.7557319223985893e-06, 2.7557319223985888e-07,
-                              2.5052108385441720e-08, 2.0876756987868100e-09, 1.6059043836821613e-10};
-        if (st < EXP0) {
-            if (KIND != GPX_MATERN52) {
-                const double F = (KIND == GPX_RBF) ? -0.5 : -2.0;
-#pragma unroll
-                for (int i = 0; i < N; ++i) x[i] = F * v[i];
-                return;
-            }
-#pragma unroll
-            for (int i = 0; i < N; ++i) {
-                switch (st) {
-                    case 0: x[i] = v[i] + 1e-12; break;
-                    case 1:
-                        asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(p[i]) : "d"(x[i]));
-                        q[i] = 0.5 * x[i];
-                        break;
-                    case 2: case 5: pl[i] = p[i] * p[i]; break;
-                    case 3: case 6: pl[i] = fma(-q[i], pl[i], 1.5); break;
-                    case 4: case 7: p[i] = p[i] * pl[i]; break;
-                    case 8: pl[i] = x[i] * p[i]; break;
-                    case 9: q[i] = fma(-pl[i], pl[i], x[i]); break;
-                    case 10: p[i] = 0.5 * p[i]; break;
-                    case 11: pl[i] = fma(q[i], p[i], pl[i]); break;
-                    case 12: x[i] = GPX_SQRT5 * pl[i]; break;
-                    case 13: pl[i] = 1.0 + x[i]; break;
-                    case 14: pl[i] = fma(GPX_5_3, v[i], pl[i]); break;
-                    case 15: pl[i] = scale * pl[i]; break;
-                    default: x[i] = -x[i]; break;   // 16
-                }
-            }
-            return;
-        }
-        const int e = st - EXP0;
+        constexpr double c[14] = {1.0, 1.0, 0.5, 1.6666666666666666e-01, 4.1666666666666664e-02,
+                                  8.3333333333333332e-03, 1.3888888888888889e-03, 1.9841269841269841e-04,
+                                  2.4801587301587302e-05, 2.7557319223985893e-06, 2.7557319223985888e-07,
+                                  2.5052108385441720e-08, 2.0876756987868100e-09, 1.6059043836821613e-10};
+        constexpr int e = st - EXP0;
 #pragma unroll
         for (int i = 0; i < N; ++i) {
-            if (e == 0) x[i] = fmax(x[i], -1000.0);
-            else if (e == 1) p[i] = fma(x[i], L2E, SHIFT);
-            else if (e == 2) { ni[i] = __double2loint(p[i]); q[i] = p[i] - SHIFT; }
-            else if (e == 3) x[i] = fma(q[i], -LN2_HI, x[i]);
-            else if (e == 4) x[i] = fma(q[i], -LN2_LO, x[i]);
-            else if (e == 5) p[i] = fma(c[13], x[i], c[12]);
-            else if (e <= 17) p[i] = fma(p[i], x[i], c[17 - e]);
-            else if (e == 18) p[i] *= __hiloint2double(((ni[i] >> 1) + 1023) << 20, 0);
-            else if (e == 19) x[i] = p[i] * __hiloint2double(((ni[i] - (ni[i] >> 1)) + 1023) << 20, 0);
-            else v[i] = (KIND == GPX_MATERN52) ? pl[i] * x[i] : scale * x[i];   // 20: final
+            if constexpr (st < EXP0 && KIND != GPX_MATERN52) {
+                x[i] = ((KIND == GPX_RBF) ? -0.5 : -2.0) * v[i];
+            } else if constexpr (st < EXP0) {
+                if constexpr (st == 0) x[i] = v[i] + 1e-12;
+                else if constexpr (st == 1) {
+                    asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(p[i]) : "d"(x[i]));
+                    q[i] = 0.5 * x[i];
+                }
+                else if constexpr (st == 2 || st == 5) pl[i] = p[i] * p[i];
+                else if constexpr (st == 3 || st == 6) pl[i] = fma(-q[i], pl[i], 1.5);
+                else if constexpr (st == 4 || st == 7) p[i] = p[i] * pl[i];
+                else if constexpr (st == 8) pl[i] = x[i] * p[i];
+                else if constexpr (st == 9) q[i] = fma(-pl[i], pl[i], x[i]);
+                else if constexpr (st == 10) p[i] = 0.5 * p[i];
+                else if constexpr (st == 11) pl[i] = fma(q[i], p[i], pl[i]);
+                else if constexpr (st == 12) x[i] = GPX_SQRT5 * pl[i];
+                else if constexpr (st == 13) pl[i] = 1.0 + x[i];
+                else if constexpr (st == 14) pl[i] = fma(GPX_5_3, v[i], pl[i]);
+                else if constexpr (st == 15) pl[i] = scale * pl[i];
+                else x[i] = -x[i];   // 16
+            } else {
+                if constexpr (e == 0) x[i] = fmax(x[i], -1000.0);
+                else if constexpr (e == 1) p[i] = fma(x[i], L2E, SHIFT);
+                else if constexpr (e == 2) { ni[i] = __double2loint(p[i]); q[i] = p[i] - SHIFT; }
+                else if constexpr (e == 3) x[i] = fma(q[i], -LN2_HI, x[i]);
+                else if constexpr (e == 4) x[i] = fma(q[i], -LN2_LO, x[i]);
+                else if constexpr (e == 5) p[i] = fma(c[13], x[i], c[12]);
+                else if constexpr (e >= 6 && e <= 17) p[i] = fma(p[i], x[i], c[(e >= 6 && e <= 17) ? 17 - e : 0]);
+                else if constexpr (e == 18) p[i] *= __hiloint2double(((ni[i] >> 1) + 1023) << 20, 0);
+                else if constexpr (e == 19) x[i] = p[i] * __hiloint2double(((ni[i] - (ni[i] >> 1)) + 1023) << 20, 0);
+                else v[i] = (KIND == GPX_MATERN52) ? pl[i] * x[i] : scale * x[i];   // 20: final
+            }
         }
     }
-    // steps [lo, hi)
-    __device__ __forceinline__ void run(int lo, int hi, double scale) {
-#pragma unroll
-        for (int st = lo; st < hi; ++st) step(st, scale);
+    // steps [LO, HI)
+    template <int LO, int HI>
+    __device__ __forceinline__ void run(double scale) {
+        if constexpr (LO < HI) {
+            step<LO>(scale);
+            run<LO + 1, HI>(scale);
+        }
     }
 };
 

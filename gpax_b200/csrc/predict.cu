@@ -32,15 +32,17 @@
 // The scaled training inputs (x / length, their squared norms) and alpha are
 // staged once per call into a small workspace xs[S][n][d+2] by a prep kernel.
 #include <cuda.h>
+#include <cstdlib>
 #include "predict_small.cuh"
 
 namespace gpx {
 
-constexpr int W_WARPS = 16;                    // every warp generates K* entries and issues DMMAs
-constexpr int W_THREADS = W_WARPS * 32;        // 512 (128 registers per thread)
+constexpr int W_WARPS = 8;                     // every warp generates K* entries and issues DMMAs
+constexpr int W_THREADS = W_WARPS * 32;        // 256 (up to 255 registers per thread)
 constexpr int W_BK = 16;                       // 128-byte rows = one swizzle span
+constexpr int W_STAGGER_NS = 700;              // see the main loop
 constexpr int W_GEN_AHEAD = 2;                 // K* slices are generated this many slices ahead
-constexpr int W_MF = 4, W_NF = 4;              // per-warp fragment grid: 32 rows x 32 candidates
+constexpr int W_MF = 8, W_NF = 4;              // per-warp fragment grid: 64 rows x 32 candidates
 
 template <int WN>
 struct WCfg {
@@ -48,13 +50,12 @@ struct WCfg {
     static constexpr int R = WM * W_MF * 8;    // W rows per pass (512 for WN = 1, 256 for WN = 2)
     static constexpr int MT = WN * W_NF * 8;   // candidates per CTA (32 / 64)
     static constexpr int NST = (R >= 512) ? 3 : 4;
-    static constexpr int LDK = MT + 4;         // K*^T slice, k-major [W_BK][LDK]
     static constexpr int W_STAGE = R * W_BK;   // doubles (R * 128 bytes, multiple of 1024)
-    static constexpr int K_STAGE = W_BK * LDK;
+    static constexpr int K_STAGE = MT * W_BK;  // K*^T slice, candidate-major [MT][W_BK], same swizzle as W
     static constexpr int BOX_ROWS = (R > 256) ? 256 : R;
     static constexpr int NBOX = R / BOX_ROWS;
     static constexpr int KSTEP = W_THREADS / MT;        // k rows generated per pass over the slice
-    static constexpr int GEN = W_BK / KSTEP;            // K* entries per thread per slice (1 / 2)
+    static constexpr int GEN = W_BK / KSTEP;            // K* entries per thread per slice (2 / 4)
     static_assert(KSTEP >= 1 && KSTEP * GEN == W_BK, "generator mapping");
     static constexpr size_t SMEM_BYTES =
         1024 /*alignment slack*/ +
@@ -122,71 +123,89 @@ predict_prep_kernel(gpx_kernel_params kp, int n, int n_pad, const double *__rest
     dst[d + 1] = alpha[(size_t)s * n + k];
 }
 
-// Half a slice (two k-steps KS0, KS0+1) of DMMAs for the fragments mi >= MI0 of
-// this warp, with the generator steps [SLO, SHI) spread evenly between them (the
-// DMMA that follows a step hides the latency of the step's result).
-// MI0 is a template parameter so that fragments above the diagonal are skipped
-// by a real branch in the caller (ptxas turns per-fragment `if`s into predicated
-// DMMAs, and a predicated-off DMMA still occupies the pipe for its 16 cycles).
-template <int MI0, int KS0, int SLO, int SHI, int WM, int LDK, class Gen>
-__device__ __forceinline__ void mma_half(double (&acc)[W_MF][W_NF][2], const double *cW,
-                                         const double *cK, const int (&offA)[W_BK / 4], Gen &gen,
-                                         double scale) {
-    constexpr int NFR = W_MF - MI0, ND = 2 * NFR * W_NF, NS = SHI - SLO;
-    if (ND == 0) {
-        gen.run(SLO, SHI, scale);
-        return;
-    }
+// Issue-slot model (measured, tools/probe + ncu): on B200 a DMMA.8x8x4 holds the
+// sub-partition's dispatch port for its 16 cycles, an FP64 ALU instruction for 2
+// and anything else for 1, and nothing overlaps.  Kernel time is therefore
+//   16 * #DMMA + 2 * #FP64 + #other   per sub-partition,
+// so the main loop is written to minimise the instructions that are not DMMAs:
+//   * k-permuted fragments: the DMMA k-step ks multiplies k = {ks, 4+ks, 8+ks, 12+ks}
+//     of the 16-wide slice (any k order is valid as long as A and B agree), so one
+//     lane's four A (or B) values of a slice are 32 contiguous bytes = 2 x LDS.128;
+//   * W slab and K* slice share the 128-byte XOR swizzle (TMA writes W in it, the
+//     generator writes K* in it), which makes those LDS.128 conflict-free;
+//   * generator steps sit between the DMMAs of the same warp, one instruction
+//     deep, so their latency is covered by the DMMA that follows.
+
+// One slice of DMMAs for the fragments mi >= MI0 of this warp with the generator
+// steps [0, NS) spread evenly between them.  offAB[h] is the lane's swizzled
+// offset (in doubles) of k-pair h (k = 4 lc + 2h, +1) inside an 8-row group;
+// the row-group bases are added here.  MI0 is a template parameter so that
+// fragments above the diagonal are skipped by a real branch in the caller (ptxas
+// turns per-fragment `if`s into predicated DMMAs, and a predicated-off DMMA
+// still occupies the pipe for its 16 cycles).
+template <int MI0, int WM, int DBG, class Gen>
+__device__ __forceinline__ void mma_slice(double (&acc)[W_MF][W_NF][2], const double *cW,
+                                          const double *cK, const int (&offAB)[2], Gen &gen,
+                                          double scale) {
+    constexpr int NFR = W_MF - MI0, ND = NFR * W_NF * 4, NS = Gen::NSTEPS;
+    if constexpr (ND == 0 || (DBG & 2) != 0) {
+        if constexpr (!(DBG & 1)) gen.template run<0, NS>(scale);
+    } else {
+        double2 a, b[W_NF];
+        static_for<ND>([&](auto J) {
+            constexpr int j = decltype(J)::value;
+            constexpr int ni = j % W_NF, e = (j / W_NF) % 2, fi = (j / (2 * W_NF)) % NFR,
+                          h = j / (2 * W_NF * NFR), mi = MI0 + fi;
+            if constexpr (fi == 0 && e == 0 && ni == 0) {       // k-steps 2h and 2h+1 start
 #pragma unroll
-    for (int kk = 0; kk < 2; ++kk) {
-        const int ks = KS0 + kk;
-        double b[W_NF];
-#pragma unroll
-        for (int ni = 0; ni < W_NF; ++ni) b[ni] = cK[ks * 4 * LDK + ni * 8];
-#pragma unroll
-        for (int mi = MI0; mi < W_MF; ++mi) {
-            const double a = cW[mi * (WM * 8 * W_BK) + offA[ks]];
-#pragma unroll
-            for (int ni = 0; ni < W_NF; ++ni) {
-                dmma884(acc[mi][ni][0], acc[mi][ni][1], a, b[ni]);
-                const int j = (kk * NFR + (mi - MI0)) * W_NF + ni;
-                gen.run(SLO + (j * NS) / ND, SLO + ((j + 1) * NS) / ND, scale);
+                for (int q = 0; q < W_NF; ++q)
+                    b[q] = *reinterpret_cast<const double2 *>(cK + q * (8 * W_BK) + offAB[h]);
             }
-        }
+            if constexpr (e == 0 && ni == 0)
+                a = *reinterpret_cast<const double2 *>(cW + mi * (WM * 8 * W_BK) + offAB[h]);
+            dmma884(acc[mi][ni][0], acc[mi][ni][1], e ? a.y : a.x, e ? b[ni].y : b[ni].x);
+            if constexpr (!(DBG & 1)) gen.template run<(j * NS) / ND, ((j + 1) * NS) / ND>(scale);
+        });
     }
 }
 
-template <int KS0, int SLO, int SHI, int WM, int LDK, class Gen>
-__device__ __forceinline__ void mma_half_from(int mi0, double (&acc)[W_MF][W_NF][2],
-                                              const double *cW, const double *cK,
-                                              const int (&offA)[W_BK / 4], Gen &gen, double scale) {
+template <int WM, int DBG, class Gen>
+__device__ __forceinline__ void mma_slice_from(int mi0, double (&acc)[W_MF][W_NF][2],
+                                               const double *cW, const double *cK,
+                                               const int (&offAB)[2], Gen &gen, double scale) {
     switch (mi0) {
-        case 0: mma_half<0, KS0, SLO, SHI, WM, LDK>(acc, cW, cK, offA, gen, scale); break;
-        case 1: mma_half<1, KS0, SLO, SHI, WM, LDK>(acc, cW, cK, offA, gen, scale); break;
-        case 2: mma_half<2, KS0, SLO, SHI, WM, LDK>(acc, cW, cK, offA, gen, scale); break;
-        case 3: mma_half<3, KS0, SLO, SHI, WM, LDK>(acc, cW, cK, offA, gen, scale); break;
-        default: mma_half<4, KS0, SLO, SHI, WM, LDK>(acc, cW, cK, offA, gen, scale); break;
+        case 0: mma_slice<0, WM, DBG>(acc, cW, cK, offAB, gen, scale); break;
+        case 1: mma_slice<1, WM, DBG>(acc, cW, cK, offAB, gen, scale); break;
+        case 2: mma_slice<2, WM, DBG>(acc, cW, cK, offAB, gen, scale); break;
+        case 3: mma_slice<3, WM, DBG>(acc, cW, cK, offAB, gen, scale); break;
+        case 4: mma_slice<4, WM, DBG>(acc, cW, cK, offAB, gen, scale); break;
+        case 5: mma_slice<5, WM, DBG>(acc, cW, cK, offAB, gen, scale); break;
+        case 6: mma_slice<6, WM, DBG>(acc, cW, cK, offAB, gen, scale); break;
+        case 7: mma_slice<7, WM, DBG>(acc, cW, cK, offAB, gen, scale); break;
+        default: mma_slice<8, WM, DBG>(acc, cW, cK, offAB, gen, scale); break;
     }
 }
 
 // ---------------------------------------------------------------------------
 // main kernel
+// DBG (profiling experiments only, GPX_PREDICT_DEBUG): bit 0 skips the generator
+// arithmetic, bit 1 the DMMAs, bit 2 the TMA loads.
 // ---------------------------------------------------------------------------
-template <int KIND, int WN>
+template <int KIND, int WN, int DBG = 0>
 __global__ void __launch_bounds__(W_THREADS, 1)
 predict_ws_kernel(const __grid_constant__ CUtensorMap tmW, gpx_kernel_params kp, int n, int n_pad,
                   int M, const double *__restrict__ xs, const double *__restrict__ xnew,
                   const double *__restrict__ m_new, double m_const,
                   const double *__restrict__ diag_add, double *__restrict__ mu,
-                  double *__restrict__ var) {
+                  double *__restrict__ var, unsigned stagger_ns) {
     using C = WCfg<WN>;
     constexpr int WM = C::WM, GEN = C::GEN, KSTEP = C::KSTEP, D = W_GEN_AHEAD;
     extern __shared__ unsigned char smem_raw[];
-    // 1024-byte alignment: the 128-byte TMA swizzle pattern is a function of the
+    // 1024-byte alignment: the 128-byte swizzle pattern is a function of the
     // shared-memory address bits [4:9]
     // (offset arithmetic on the array itself keeps the shared address space -> LDS, not LD)
     double *sW = reinterpret_cast<double *>(smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u));
-    double *sK = sW + (size_t)C::NST * C::W_STAGE;        // [NST][W_BK][LDK]
+    double *sK = sW + (size_t)C::NST * C::W_STAGE;        // [NST][MT][W_BK] swizzled
     double *sZ = sK + (size_t)C::NST * C::K_STAGE;        // [MT][MAX_D+1]
     double *colsum = sZ + C::MT * (GPX_MAX_D + 1);        // [MT]
     double *wpart = colsum + C::MT;                       // [WM][MT]
@@ -259,6 +278,13 @@ predict_ws_kernel(const __grid_constant__ CUtensorMap tmW, gpx_kernel_params kp,
     double macc = 0.0;
 #pragma unroll
     for (int i = 0; i < GEN; ++i) xval[i] = __ldg(xrow + (size_t)(i * KSTEP) * XS);
+    // swizzled K* offsets of this thread's entries: (col, k) -> col*16 + (((k/2) ^ (col&7)) * 2) + (k&1)
+    int offK[GEN];
+#pragma unroll
+    for (int i = 0; i < GEN; ++i) {
+        const int k = g_k0 + i * KSTEP;
+        offK[i] = g_j * W_BK + ((((k >> 1) ^ (g_j & 7))) << 1) + (k & 1);
+    }
 
     // gen_begin: distances of this thread's GEN entries of slice gi (registers only)
     auto gen_begin = [&](Gen &g, double (&al)[GEN]) {
@@ -289,6 +315,10 @@ predict_ws_kernel(const __grid_constant__ CUtensorMap tmW, gpx_kernel_params kp,
     auto tma_issue = [&]() {
         const uint32_t gst = gi % C::NST, gph = (gi / C::NST) & 1;
         mbar_wait(bar_empty + 8 * gst, gph ^ 1);
+        if (DBG & 4) {
+            mbar_arrive(bar_fullW + 8 * gst);
+            return;
+        }
         mbar_arrive_expect_tx(bar_fullW + 8 * gst, (uint32_t)(C::W_STAGE * sizeof(double)));
 #pragma unroll
         for (int b = 0; b < C::NBOX; ++b)
@@ -299,11 +329,11 @@ predict_ws_kernel(const __grid_constant__ CUtensorMap tmW, gpx_kernel_params kp,
     auto gen_end = [&](Gen &g, double (&al)[GEN]) {
         const uint32_t gst = gi % C::NST, gph = (gi / C::NST) & 1;
         mbar_wait(bar_empty + 8 * gst, gph ^ 1);
-        double *dst = sK + (size_t)gst * C::K_STAGE + g_k0 * C::LDK + g_j;
+        double *dst = sK + (size_t)gst * C::K_STAGE;
         const bool do_mean = (g_rb == NRB - 1);
 #pragma unroll
         for (int i = 0; i < GEN; ++i) {
-            dst[i * KSTEP * C::LDK] = g.v[i];
+            dst[offK[i]] = g.v[i];
             if (do_mean) macc = fma(g.v[i], al[i], macc);
         }
         __syncwarp();
@@ -321,16 +351,16 @@ predict_ws_kernel(const __grid_constant__ CUtensorMap tmW, gpx_kernel_params kp,
         double al[GEN];
         if (t == 0) tma_issue();
         gen_begin(g, al);
-        g.run(0, NS, scale);
+        if (!(DBG & 1)) g.template run<0, NS>(scale);
         gen_end(g, al);
     }
 
-    // swizzled A-fragment offsets: row = 8 f + lr, 16-byte chunk (2 ks + lc/2) ^ lr
-    int offA[W_BK / 4];
+    // lane's swizzled offset of k-pair h (k = 4 lc + 2h, +1) inside its 8-row group:
+    // row lr, 16-byte chunk (2 lc + h) ^ lr; identical for the W slab and the K* slice
+    int offAB[2];
 #pragma unroll
-    for (int ks = 0; ks < W_BK / 4; ++ks)
-        offA[ks] = (wm * 8 + lr) * W_BK + ((((ks << 1) | (lc >> 1)) ^ lr) << 1) + (lc & 1);
-    const int offB = lc * C::LDK + wn * 32 + lr;
+    for (int h = 0; h < 2; ++h) offAB[h] = lr * W_BK + ((((lc << 1) | h) ^ lr) << 1);
+    const int baseA = wm * 8 * W_BK, baseB = wn * 32 * W_BK;
 
     double acc[W_MF][W_NF][2];
 #pragma unroll
@@ -340,9 +370,16 @@ predict_ws_kernel(const __grid_constant__ CUtensorMap tmW, gpx_kernel_params kp,
 
     uint32_t st = 0, ph = 0;          // stage / phase of the slice being multiplied
     for (int rb = 0; rb < NRB; ++rb) {
+        // Stagger the two warps of each SM sub-partition (w and w + 4) by about half a
+        // slice: they would otherwise run in lock-step (both in the non-DMMA part of the
+        // loop, then both contending for the DMMA pipe).  Offset by half a period, one
+        // warp's DMMAs cover the other's barrier / staging / generator bookkeeping.  The
+        // offset survives until the next CTA-wide barrier (end of the row block).
+        if (stagger_ns > 0 && warp >= W_WARPS / 2) __nanosleep(stagger_ns);
         const int kd0 = rb * C::R;
         const int kend = (n < kd0 + C::R) ? n : kd0 + C::R;
         const int nsl = (kend + W_BK - 1) / W_BK;
+        const int nsl_full = kd0 / W_BK;
         // fragments that hold rows < n in this block: f < fr_lim  <=>  mi < mi_lim
         const int fr_lim = (kend - kd0 + 7) >> 3;
         const int mi_lim = (fr_lim - wm + WM - 1) / WM;
@@ -358,39 +395,38 @@ predict_ws_kernel(const __grid_constant__ CUtensorMap tmW, gpx_kernel_params kp,
             }
             mbar_wait(bar_fullW + 8 * st, ph);
             mbar_wait(bar_fullK + 8 * st, ph);
-            const double *cW = sW + (size_t)st * C::W_STAGE;
-            const double *cK = sK + (size_t)st * C::K_STAGE + offB;
-            const int kl = c * W_BK - kd0;
+            const double *cW = sW + (size_t)st * C::W_STAGE + baseA;
+            const double *cK = sK + (size_t)st * C::K_STAGE + baseB;
             if (mi_lim >= W_MF) {
-                // fragment f = wm + WM*mi is needed for k-steps starting below 8*(f+1):
-                // first fragment index per half slice (0 below the diagonal block)
-                int mi0a = 0, mi0b = 0;
-                if (kl >= 0) {
-                    const int fa = kl >> 3, fb = fa + 1;
-                    mi0a = fa <= wm ? 0 : (fa - wm + WM - 1) / WM;
-                    mi0b = fb <= wm ? 0 : (fb - wm + WM - 1) / WM;
+                if (c < nsl_full) {
+                    mma_slice<0, WM, DBG>(acc, cW, cK, offAB, g, scale);
+                } else {
+                    // diagonal block: fragment f = wm + WM*mi holds rows 8f..8f+7 and needs the
+                    // slice starting at local column kl iff 8f + 7 >= kl (W is zero above its diagonal)
+                    const int fa = (c * W_BK - kd0) >> 3;
+                    const int mi0 = fa <= wm ? 0 : (fa - wm + WM - 1) / WM;
+                    mma_slice_from<WM, DBG>(mi0, acc, cW, cK, offAB, g, scale);
                 }
-                mma_half_from<0, 0, NS / 2, WM, C::LDK>(mi0a, acc, cW, cK, offA, g, scale);
-                mma_half_from<2, NS / 2, NS, WM, C::LDK>(mi0b, acc, cW, cK, offA, g, scale);
             } else {
-                g.run(0, NS, scale);
                 // ragged last row block (n not a multiple of R): predicated fragments
+                if (!(DBG & 1)) g.template run<0, NS>(scale);
+                const int fa = (c * W_BK - kd0) >> 3;     // may be negative
+                int mi0 = fa <= wm ? 0 : (fa - wm + WM - 1) / WM;
 #pragma unroll
-                for (int ks = 0; ks < W_BK / 4; ++ks) {
-                    const int fmin = (kl + ks * 4) >> 3;                 // may be negative
-                    int mi0 = (fmin - wm + WM - 1) / WM;
-                    mi0 = (fmin - wm) <= 0 ? 0 : mi0;
-                    if (mi0 >= mi_lim) continue;
-                    double b[W_NF];
+                for (int h = 0; h < 2; ++h) {
+                    double2 b[W_NF];
 #pragma unroll
-                    for (int ni = 0; ni < W_NF; ++ni) b[ni] = cK[ks * 4 * C::LDK + ni * 8];
+                    for (int ni = 0; ni < W_NF; ++ni)
+                        b[ni] = *reinterpret_cast<const double2 *>(cK + ni * (8 * W_BK) + offAB[h]);
 #pragma unroll
                     for (int mi = 0; mi < W_MF; ++mi) {
                         if (mi >= mi0 && mi < mi_lim) {
-                            const double a = cW[mi * (WM * 8 * W_BK) + offA[ks]];
+                            const double2 a = *reinterpret_cast<const double2 *>(cW + mi * (WM * 8 * W_BK) + offAB[h]);
 #pragma unroll
-                            for (int ni = 0; ni < W_NF; ++ni)
-                                dmma884(acc[mi][ni][0], acc[mi][ni][1], a, b[ni]);
+                            for (int ni = 0; ni < W_NF; ++ni) {
+                                dmma884(acc[mi][ni][0], acc[mi][ni][1], a.x, b[ni].x);
+                                dmma884(acc[mi][ni][0], acc[mi][ni][1], a.y, b[ni].y);
+                            }
                         }
                     }
                 }
@@ -504,8 +540,25 @@ static int launch_predict_ws(const gpx_kernel_params *kp, int64_t S, int64_t n, 
     if (rc) return rc;
     dim3 grid((unsigned)((M + C::MT - 1) / C::MT), (unsigned)S);
     const int n_pad = (int)((n + W_BK - 1) / W_BK * W_BK);
+    static int stagger = -1;
+    if (stagger < 0) { const char *e = getenv("GPX_STAGGER_NS"); stagger = e ? atoi(e) : W_STAGGER_NS; }
+#ifdef GPX_PREDICT_DEBUG_VARIANTS
+    if (KIND == GPX_MATERN52 && WN == 1) {
+        static int dbg = -1;
+        if (dbg < 0) { const char *e = getenv("GPX_PREDICT_DEBUG"); dbg = e ? atoi(e) : 0; }
+#define GPX_DBG_CASE(D)                                                                            \
+        case D: {                                                                                  \
+            static bool cfg = false;                                                               \
+            if (!cfg) { cudaFuncSetAttribute(predict_ws_kernel<GPX_MATERN52, 1, D>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::SMEM_BYTES); cfg = true; } \
+            predict_ws_kernel<GPX_MATERN52, 1, D><<<grid, W_THREADS, C::SMEM_BYTES, st>>>(         \
+                tm, *kp, (int)n, n_pad, (int)M, xs, xnew, m_new, m_const, diag_add, mu, var, stagger); \
+            return 0; }
+        switch (dbg) { GPX_DBG_CASE(1) GPX_DBG_CASE(2) GPX_DBG_CASE(3) default: break; }
+#undef GPX_DBG_CASE
+    }
+#endif
     predict_ws_kernel<KIND, WN><<<grid, W_THREADS, C::SMEM_BYTES, st>>>(
-        tm, *kp, (int)n, n_pad, (int)M, xs, xnew, m_new, m_const, diag_add, mu, var);
+        tm, *kp, (int)n, n_pad, (int)M, xs, xnew, m_new, m_const, diag_add, mu, var, stagger);
     return 0;
 }
 
