@@ -200,6 +200,14 @@ __device__ __forceinline__ void static_for(F &&f) {
 // DMMAs: the DMMA that follows hides the latency of the step's result.
 //   RBF / PERIODIC : v = clipped r2 (or the periodic sum)  -> scale * exp(F * v), F = -0.5 / -2
 //   MATERN52       : v = clipped r2 -> scale * (1 + s + 5/3 r2) * exp(-s), s = sqrt5 * sqrt(r2 + 1e-12)
+static __constant__ double KG_C[21] = {
+    1.0, 1.0, 0.5, 1.6666666666666666e-01, 4.1666666666666664e-02, 8.3333333333333332e-03,
+    1.3888888888888889e-03, 1.9841269841269841e-04, 2.4801587301587302e-05, 2.7557319223985893e-06,
+    2.7557319223985888e-07, 2.5052108385441720e-08, 2.0876756987868100e-09, 1.6059043836821613e-10,
+    1.4426950408889634 /*log2 e*/, 6755399441055744.0 /*1.5 * 2^52*/,
+    6.93147180369123816490e-01 /*ln2 hi*/, 1.90821492927058770002e-10 /*ln2 lo*/,
+    1e-12, GPX_SQRT5, GPX_5_3};
+
 template <int KIND, int N>
 struct KGen {
     static constexpr int EXP0 = (KIND == GPX_MATERN52) ? 17 : 1;   // first step of the exp block
@@ -209,19 +217,17 @@ struct KGen {
 
     template <int st>
     __device__ __forceinline__ void step(double scale) {
-        const double L2E = 1.4426950408889634, SHIFT = 6755399441055744.0;
-        const double LN2_HI = 6.93147180369123816490e-01, LN2_LO = 1.90821492927058770002e-10;
-        constexpr double c[14] = {1.0, 1.0, 0.5, 1.6666666666666666e-01, 4.1666666666666664e-02,
-                                  8.3333333333333332e-03, 1.3888888888888889e-03, 1.9841269841269841e-04,
-                                  2.4801587301587302e-05, 2.7557319223985893e-06, 2.7557319223985888e-07,
-                                  2.5052108385441720e-08, 2.0876756987868100e-09, 1.6059043836821613e-10};
+        // constants come from the constant bank (an FP64 operand c[bank][off] costs nothing,
+        // a 64-bit immediate costs two UMOVs each time it is rematerialised)
+        const double *c = KG_C;
+        const double L2E = KG_C[14], SHIFT = KG_C[15], LN2_HI = KG_C[16], LN2_LO = KG_C[17];
         constexpr int e = st - EXP0;
 #pragma unroll
         for (int i = 0; i < N; ++i) {
             if constexpr (st < EXP0 && KIND != GPX_MATERN52) {
                 x[i] = ((KIND == GPX_RBF) ? -0.5 : -2.0) * v[i];
             } else if constexpr (st < EXP0) {
-                if constexpr (st == 0) x[i] = v[i] + 1e-12;
+                if constexpr (st == 0) x[i] = v[i] + KG_C[18];
                 else if constexpr (st == 1) {
                     asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(p[i]) : "d"(x[i]));
                     q[i] = 0.5 * x[i];
@@ -233,9 +239,9 @@ struct KGen {
                 else if constexpr (st == 9) q[i] = fma(-pl[i], pl[i], x[i]);
                 else if constexpr (st == 10) p[i] = 0.5 * p[i];
                 else if constexpr (st == 11) pl[i] = fma(q[i], p[i], pl[i]);
-                else if constexpr (st == 12) x[i] = GPX_SQRT5 * pl[i];
+                else if constexpr (st == 12) x[i] = KG_C[19] * pl[i];
                 else if constexpr (st == 13) pl[i] = 1.0 + x[i];
-                else if constexpr (st == 14) pl[i] = fma(GPX_5_3, v[i], pl[i]);
+                else if constexpr (st == 14) pl[i] = fma(KG_C[20], v[i], pl[i]);
                 else if constexpr (st == 15) pl[i] = scale * pl[i];
                 else x[i] = -x[i];   // 16
             } else {

@@ -40,8 +40,8 @@ namespace gpx {
 constexpr int W_WARPS = 8;                     // every warp generates K* entries and issues DMMAs
 constexpr int W_THREADS = W_WARPS * 32;        // 256 (up to 255 registers per thread)
 constexpr int W_BK = 16;                       // 128-byte rows = one swizzle span
-constexpr int W_STAGGER_NS = 700;              // see the main loop
 constexpr int W_GEN_AHEAD = 2;                 // K* slices are generated this many slices ahead
+constexpr int W_NK = 5;                        // K* ring slots (>= GEN_AHEAD + 2: no "empty" barrier needed)
 constexpr int W_MF = 8, W_NF = 4;              // per-warp fragment grid: 64 rows x 32 candidates
 
 template <int WN>
@@ -54,17 +54,18 @@ struct WCfg {
     static constexpr int K_STAGE = MT * W_BK;  // K*^T slice, candidate-major [MT][W_BK], same swizzle as W
     static constexpr int BOX_ROWS = (R > 256) ? 256 : R;
     static constexpr int NBOX = R / BOX_ROWS;
-    static constexpr int KSTEP = W_THREADS / MT;        // k rows generated per pass over the slice
-    static constexpr int GEN = W_BK / KSTEP;            // K* entries per thread per slice (2 / 4)
-    static_assert(KSTEP >= 1 && KSTEP * GEN == W_BK, "generator mapping");
+    static constexpr int GEN = MT / 16;        // K* entries per thread per slice: k = t % 16, j = t / 16 + 16 i
     static constexpr size_t SMEM_BYTES =
         1024 /*alignment slack*/ +
-        sizeof(double) * ((size_t)NST * W_STAGE + (size_t)NST * K_STAGE + MT * (GPX_MAX_D + 1) +
-                          MT /*colsum*/ + WM * MT /*wpart*/ + W_THREADS /*smean*/ + 2 * GPX_MAX_D) +
-        sizeof(uint64_t) * 3 * NST;
+        sizeof(double) * ((size_t)NST * W_STAGE + (size_t)W_NK * K_STAGE + MT * (GPX_MAX_D + 1) +
+                          MT /*colsum*/ + WM * MT /*wpart*/ + W_THREADS * GEN /*smean*/ + 2 * GPX_MAX_D) +
+        sizeof(uint64_t) * (2 * NST + W_NK);
 };
 
-// ---- mbarrier / TMA primitives (PTX) ---------------------------------------
+// workspace row: DMAX scaled coordinates (zero padded), squared norm, alpha
+__host__ __device__ constexpr int dmax_of(int d) { return d <= 2 ? 2 : (d <= 4 ? 4 : 8); }
+
+// ---- mbarrier / TMA / shared-memory primitives (PTX) -------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void *p) {
     return (uint32_t)__cvta_generic_to_shared(p);
 }
@@ -95,9 +96,20 @@ __device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap *tm,
         "[%0], [%1, {%3, %4, %5}], [%2];\n" ::"r"(dst), "l"(tm), "r"(bar), "r"(c0), "r"(c1), "r"(c2)
         : "memory");
 }
+// 16-byte shared load at a 32-bit shared address (+ compile-time byte offset -> LDS.128 [R+imm])
+__device__ __forceinline__ double2 lds128(uint32_t addr) {
+    double2 v;
+    asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];\n" : "=d"(v.x), "=d"(v.y) : "r"(addr));
+    return v;
+}
+__device__ __forceinline__ void sts64(uint32_t addr, double v) {
+    asm volatile("st.shared.f64 [%0], %1;\n" ::"r"(addr), "d"(v) : "memory");
+}
+
 // ---------------------------------------------------------------------------
-// prep: xs[s][k][0..d-1] = x_k / length_s (raw x for PERIODIC), [d] = squared
-// norm of the scaled point, [d+1] = alpha_s[k]; k < n_pad = n rounded up to W_BK
+// prep: xs[s][k][0..DMAX-1] = x_k / length_s (raw x for PERIODIC; zero beyond d),
+// [DMAX] = squared norm of the scaled point, [DMAX+1] = alpha_s[k];
+// k < n_pad = n rounded up to W_BK (padding rows are all zero)
 // ---------------------------------------------------------------------------
 template <int KIND>
 __global__ void __launch_bounds__(256)
@@ -106,12 +118,10 @@ predict_prep_kernel(gpx_kernel_params kp, int n, int n_pad, const double *__rest
     const int64_t s = blockIdx.y;
     const int k = blockIdx.x * 256 + threadIdx.x;
     if (k >= n_pad) return;
-    const int d = kp.d, XS = d + 2;
-    double *dst = xs + ((size_t)s * n_pad + k) * XS;
-    if (k >= n) {            // padding rows: finite values, alpha = 0 (W columns >= n read as 0)
-        for (int q = 0; q < XS; ++q) dst[q] = 0.0;
-        return;
-    }
+    const int d = kp.d, DM = dmax_of(d), XSP = DM + 2;
+    double *dst = xs + ((size_t)s * n_pad + k) * XSP;
+    for (int q = 0; q < XSP; ++q) dst[q] = 0.0;
+    if (k >= n) return;      // padding rows: finite values, alpha = 0 (W columns >= n read as 0)
     double nrm = 0.0;
     for (int q = 0; q < d; ++q) {
         double v = x[(size_t)k * d + q];
@@ -119,51 +129,64 @@ predict_prep_kernel(gpx_kernel_params kp, int n, int n_pad, const double *__rest
         dst[q] = v;
         nrm += v * v;
     }
-    dst[d] = nrm;
-    dst[d + 1] = alpha[(size_t)s * n + k];
+    dst[DM] = nrm;
+    dst[DM + 1] = alpha[(size_t)s * n + k];
 }
 
-// Issue-slot model (measured, tools/probe + ncu): on B200 a DMMA.8x8x4 holds the
-// sub-partition's dispatch port for its 16 cycles, an FP64 ALU instruction for 2
-// and anything else for 1, and nothing overlaps.  Kernel time is therefore
-//   16 * #DMMA + 2 * #FP64 + #other   per sub-partition,
-// so the main loop is written to minimise the instructions that are not DMMAs:
+// Issue-slot model (measured, tools/probe + ncu ablations): on B200 a DMMA.8x8x4
+// holds the sub-partition's dispatch port for its 16 cycles, an FP64 ALU
+// instruction for 2 and anything else for about 1, and nothing overlaps: kernel
+// time is close to  16 * #DMMA + 2 * #FP64 + #other  per sub-partition (removing
+// the generator or the DMMAs from the kernel removes exactly their share).  The
+// main loop is therefore written to minimise the instructions that are not DMMAs:
 //   * k-permuted fragments: the DMMA k-step ks multiplies k = {ks, 4+ks, 8+ks, 12+ks}
 //     of the 16-wide slice (any k order is valid as long as A and B agree), so one
 //     lane's four A (or B) values of a slice are 32 contiguous bytes = 2 x LDS.128;
 //   * W slab and K* slice share the 128-byte XOR swizzle (TMA writes W in it, the
 //     generator writes K* in it), which makes those LDS.128 conflict-free;
+//   * shared loads are PTX ld.shared with register base + immediate offsets;
 //   * generator steps sit between the DMMAs of the same warp, one instruction
-//     deep, so their latency is covered by the DMMA that follows.
+//     deep, so their latency is covered by the DMMA that follows; their constants
+//     come from the constant bank (no 64-bit immediates to materialise);
+//   * the K* ring has 5 slots: a slot written for slice i+2 last held slice i-3,
+//     and every warp finished slice i-2 before anyone could pass the fullK
+//     barrier of slice i (its arrivals happen after the MMA of slice i-2), so K*
+//     stores need no "empty" barrier; only the elected TMA thread waits for the W
+//     stage to be released.
 
 // One slice of DMMAs for the fragments mi >= MI0 of this warp with the generator
-// steps [0, NS) spread evenly between them.  offAB[h] is the lane's swizzled
-// offset (in doubles) of k-pair h (k = 4 lc + 2h, +1) inside an 8-row group;
-// the row-group bases are added here.  MI0 is a template parameter so that
-// fragments above the diagonal are skipped by a real branch in the caller (ptxas
-// turns per-fragment `if`s into predicated DMMAs, and a predicated-off DMMA
-// still occupies the pipe for its 16 cycles).
+// steps [0, NS) spread evenly between them.  aAddr[h] / bAddr[h]: shared address
+// of the lane's k-pair h (k = 4 lc + 2h, +1) in fragment row-group 0 of the warp.
+// MI0 is a template parameter so that fragments above the diagonal are skipped
+// by a real branch in the caller (ptxas turns per-fragment `if`s into predicated
+// DMMAs, and a predicated-off DMMA still occupies the pipe for its 16 cycles).
 template <int MI0, int WM, int DBG, class Gen>
-__device__ __forceinline__ void mma_slice(double (&acc)[W_MF][W_NF][2], const double *cW,
-                                          const double *cK, const int (&offAB)[2], Gen &gen,
-                                          double scale) {
+__device__ __forceinline__ void mma_slice(double (&acc)[W_MF][W_NF][2], const uint32_t (&aAddr)[2],
+                                          const uint32_t (&bAddr)[2], Gen &gen, double scale) {
     constexpr int NFR = W_MF - MI0, ND = NFR * W_NF * 4, NS = Gen::NSTEPS;
+    constexpr uint32_t A_FRAG = WM * 8 * W_BK * 8, B_FRAG = 8 * W_BK * 8;   // bytes between fragments
     if constexpr (ND == 0 || (DBG & 2) != 0) {
         if constexpr (!(DBG & 1)) gen.template run<0, NS>(scale);
     } else {
-        double2 a, b[W_NF];
+        double2 a, an, b[2][W_NF];
+#pragma unroll
+        for (int q = 0; q < W_NF; ++q) b[0][q] = lds128(bAddr[0] + q * B_FRAG);
+        a = lds128(aAddr[0] + MI0 * A_FRAG);
         static_for<ND>([&](auto J) {
             constexpr int j = decltype(J)::value;
             constexpr int ni = j % W_NF, e = (j / W_NF) % 2, fi = (j / (2 * W_NF)) % NFR,
                           h = j / (2 * W_NF * NFR), mi = MI0 + fi;
-            if constexpr (fi == 0 && e == 0 && ni == 0) {       // k-steps 2h and 2h+1 start
+            if constexpr (e == 0 && ni == 0) {
+                // operands of the next fragment (and of the second half) one fragment ahead
+                if constexpr (fi + 1 < NFR) an = lds128(aAddr[h] + (mi + 1) * A_FRAG);
+                else if constexpr (h == 0) {
+                    an = lds128(aAddr[1] + MI0 * A_FRAG);
 #pragma unroll
-                for (int q = 0; q < W_NF; ++q)
-                    b[q] = *reinterpret_cast<const double2 *>(cK + q * (8 * W_BK) + offAB[h]);
+                    for (int q = 0; q < W_NF; ++q) b[1][q] = lds128(bAddr[1] + q * B_FRAG);
+                }
             }
-            if constexpr (e == 0 && ni == 0)
-                a = *reinterpret_cast<const double2 *>(cW + mi * (WM * 8 * W_BK) + offAB[h]);
-            dmma884(acc[mi][ni][0], acc[mi][ni][1], e ? a.y : a.x, e ? b[ni].y : b[ni].x);
+            dmma884(acc[mi][ni][0], acc[mi][ni][1], e ? a.y : a.x, e ? b[h][ni].y : b[h][ni].x);
+            if constexpr (e == 1 && ni == W_NF - 1) a = an;
             if constexpr (!(DBG & 1)) gen.template run<(j * NS) / ND, ((j + 1) * NS) / ND>(scale);
         });
     }
@@ -171,18 +194,18 @@ __device__ __forceinline__ void mma_slice(double (&acc)[W_MF][W_NF][2], const do
 
 template <int WM, int DBG, class Gen>
 __device__ __forceinline__ void mma_slice_from(int mi0, double (&acc)[W_MF][W_NF][2],
-                                               const double *cW, const double *cK,
-                                               const int (&offAB)[2], Gen &gen, double scale) {
+                                               const uint32_t (&aAddr)[2],
+                                               const uint32_t (&bAddr)[2], Gen &gen, double scale) {
     switch (mi0) {
-        case 0: mma_slice<0, WM, DBG>(acc, cW, cK, offAB, gen, scale); break;
-        case 1: mma_slice<1, WM, DBG>(acc, cW, cK, offAB, gen, scale); break;
-        case 2: mma_slice<2, WM, DBG>(acc, cW, cK, offAB, gen, scale); break;
-        case 3: mma_slice<3, WM, DBG>(acc, cW, cK, offAB, gen, scale); break;
-        case 4: mma_slice<4, WM, DBG>(acc, cW, cK, offAB, gen, scale); break;
-        case 5: mma_slice<5, WM, DBG>(acc, cW, cK, offAB, gen, scale); break;
-        case 6: mma_slice<6, WM, DBG>(acc, cW, cK, offAB, gen, scale); break;
-        case 7: mma_slice<7, WM, DBG>(acc, cW, cK, offAB, gen, scale); break;
-        default: mma_slice<8, WM, DBG>(acc, cW, cK, offAB, gen, scale); break;
+        case 0: mma_slice<0, WM, DBG>(acc, aAddr, bAddr, gen, scale); break;
+        case 1: mma_slice<1, WM, DBG>(acc, aAddr, bAddr, gen, scale); break;
+        case 2: mma_slice<2, WM, DBG>(acc, aAddr, bAddr, gen, scale); break;
+        case 3: mma_slice<3, WM, DBG>(acc, aAddr, bAddr, gen, scale); break;
+        case 4: mma_slice<4, WM, DBG>(acc, aAddr, bAddr, gen, scale); break;
+        case 5: mma_slice<5, WM, DBG>(acc, aAddr, bAddr, gen, scale); break;
+        case 6: mma_slice<6, WM, DBG>(acc, aAddr, bAddr, gen, scale); break;
+        case 7: mma_slice<7, WM, DBG>(acc, aAddr, bAddr, gen, scale); break;
+        default: mma_slice<8, WM, DBG>(acc, aAddr, bAddr, gen, scale); break;
     }
 }
 
@@ -191,26 +214,26 @@ __device__ __forceinline__ void mma_slice_from(int mi0, double (&acc)[W_MF][W_NF
 // DBG (profiling experiments only, GPX_PREDICT_DEBUG): bit 0 skips the generator
 // arithmetic, bit 1 the DMMAs, bit 2 the TMA loads.
 // ---------------------------------------------------------------------------
-template <int KIND, int WN, int DBG = 0>
+template <int KIND, int WN, int DMAX, int DBG = 0>
 __global__ void __launch_bounds__(W_THREADS, 1)
 predict_ws_kernel(const __grid_constant__ CUtensorMap tmW, gpx_kernel_params kp, int n, int n_pad,
                   int M, const double *__restrict__ xs, const double *__restrict__ xnew,
                   const double *__restrict__ m_new, double m_const,
                   const double *__restrict__ diag_add, double *__restrict__ mu,
-                  double *__restrict__ var, unsigned stagger_ns) {
+                  double *__restrict__ var) {
     using C = WCfg<WN>;
-    constexpr int WM = C::WM, GEN = C::GEN, KSTEP = C::KSTEP, D = W_GEN_AHEAD;
+    constexpr int WM = C::WM, GEN = C::GEN, D = W_GEN_AHEAD, XSP = DMAX + 2;
+    constexpr bool Z_IN_REGS = (DMAX <= 4);
     extern __shared__ unsigned char smem_raw[];
     // 1024-byte alignment: the 128-byte swizzle pattern is a function of the
     // shared-memory address bits [4:9]
-    // (offset arithmetic on the array itself keeps the shared address space -> LDS, not LD)
     double *sW = reinterpret_cast<double *>(smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u));
-    double *sK = sW + (size_t)C::NST * C::W_STAGE;        // [NST][MT][W_BK] swizzled
-    double *sZ = sK + (size_t)C::NST * C::K_STAGE;        // [MT][MAX_D+1]
+    double *sK = sW + (size_t)C::NST * C::W_STAGE;        // [W_NK][MT][W_BK] swizzled
+    double *sZ = sK + (size_t)W_NK * C::K_STAGE;          // [MT][MAX_D+1]
     double *colsum = sZ + C::MT * (GPX_MAX_D + 1);        // [MT]
     double *wpart = colsum + C::MT;                       // [WM][MT]
-    double *smean = wpart + WM * C::MT;                   // [W_THREADS]
-    double *s_len = smean + W_THREADS;                    // [MAX_D]
+    double *smean = wpart + WM * C::MT;                   // [GEN][W_THREADS]
+    double *s_len = smean + W_THREADS * C::GEN;           // [MAX_D]
     double *s_per = s_len + GPX_MAX_D;                    // [MAX_D]
     uint64_t *bars = reinterpret_cast<uint64_t *>(s_per + GPX_MAX_D);
 
@@ -219,21 +242,22 @@ predict_ws_kernel(const __grid_constant__ CUtensorMap tmW, gpx_kernel_params kp,
     const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
     const int d = kp.d;
     const double scale = kp.scale[s];
-    const uint32_t bar_fullW = smem_u32(bars), bar_fullK = smem_u32(bars + C::NST),
-                   bar_empty = smem_u32(bars + 2 * C::NST);
+    const uint32_t bar_fullW = smem_u32(bars), bar_emptyW = bar_fullW + 8 * C::NST,
+                   bar_fullK = bar_emptyW + 8 * C::NST;
 
-    if (t < d) {
-        s_len[t] = len_of(kp, s, t);
-        s_per[t] = per_of(kp, s, t);
+    if (t < GPX_MAX_D) {
+        s_len[t] = t < d ? len_of(kp, s, t) : 1.0;
+        s_per[t] = t < d ? per_of(kp, s, t) : 1.0;
     }
     if (t < C::MT) colsum[t] = 0.0;
     if (t == 0) {
 #pragma unroll
         for (int i = 0; i < C::NST; ++i) {
             mbar_init(bar_fullW + 8 * i, 1);           // the expect_tx arrive of the TMA thread
-            mbar_init(bar_fullK + 8 * i, W_WARPS);     // one elected lane per warp
-            mbar_init(bar_empty + 8 * i, W_WARPS);
+            mbar_init(bar_emptyW + 8 * i, W_WARPS);    // one elected lane per warp
         }
+#pragma unroll
+        for (int i = 0; i < W_NK; ++i) mbar_init(bar_fullK + 8 * i, W_WARPS);
         asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
         asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory");
         asm volatile("prefetch.tensormap [%0];\n" ::"l"(&tmW) : "memory");
@@ -243,8 +267,8 @@ predict_ws_kernel(const __grid_constant__ CUtensorMap tmW, gpx_kernel_params kp,
     for (int e = t; e < C::MT; e += W_THREADS) {
         const int gj = j0 + e;
         double nrm = 0.0;
-        for (int q = 0; q < d; ++q) {
-            double v = gj < M ? xnew[(size_t)gj * d + q] : 0.0;
+        for (int q = 0; q < GPX_MAX_D; ++q) {
+            double v = (gj < M && q < d) ? xnew[(size_t)gj * d + q] : 0.0;
             if (KIND != GPX_PERIODIC) v = v / s_len[q];
             sZ[e * (GPX_MAX_D + 1) + q] = v;
             nrm += v * v;
@@ -263,58 +287,84 @@ predict_ws_kernel(const __grid_constant__ CUtensorMap tmW, gpx_kernel_params kp,
 
     const int wm = warp / WN, wn = warp % WN;
     const int lr = lane >> 2, lc = lane & 3;
-    // ---- generator: thread -> candidate g_j, k rows g_k0 + i*KSTEP (g_k0 is warp-uniform) ----
+    const uint32_t sW_u = smem_u32(sW), sK_u = smem_u32(sK);
+
+    // ---- generator: thread -> k row gk of the slice, candidates jb + 16 i ----
     using Gen = KGen<KIND, GEN>;
     constexpr int NS = Gen::NSTEPS;
-    const int g_j = t % C::MT, g_k0 = t / C::MT;
-    const double *pz = sZ + g_j * (GPX_MAX_D + 1);
-    const double z2n = pz[GPX_MAX_D];
-    const int XS = d + 2;
-    // lane q < XS holds entry q of the staged training row (coords, norm, alpha) of the
-    // slice being generated; it is fetched one slice ahead and broadcast with shuffles
-    const double *xrow = xs + ((size_t)s * n_pad + g_k0) * XS + (lane < XS ? lane : 0);
-    double xval[GEN];
-    int gi = 0, g_rb = 0, g_c = 0, g_nsl = nsl_of(0);     // next slice to generate
-    double macc = 0.0;
-#pragma unroll
-    for (int i = 0; i < GEN; ++i) xval[i] = __ldg(xrow + (size_t)(i * KSTEP) * XS);
-    // swizzled K* offsets of this thread's entries: (col, k) -> col*16 + (((k/2) ^ (col&7)) * 2) + (k&1)
-    int offK[GEN];
-#pragma unroll
-    for (int i = 0; i < GEN; ++i) {
-        const int k = g_k0 + i * KSTEP;
-        offK[i] = g_j * W_BK + ((((k >> 1) ^ (g_j & 7))) << 1) + (k & 1);
-    }
-
-    // gen_begin: distances of this thread's GEN entries of slice gi (registers only)
-    auto gen_begin = [&](Gen &g, double (&al)[GEN]) {
+    const int gk = t & 15, jb = t >> 4;
+    double zr[Z_IN_REGS ? GEN : 1][Z_IN_REGS ? DMAX + 1 : 1];   // candidate coords + norm (small d)
+    double lenr[Z_IN_REGS ? DMAX : 1], perr[Z_IN_REGS ? DMAX : 1];
+    if constexpr (Z_IN_REGS) {
 #pragma unroll
         for (int i = 0; i < GEN; ++i) {
+#pragma unroll
+            for (int q = 0; q < DMAX; ++q) zr[i][q] = sZ[(jb + 16 * i) * (GPX_MAX_D + 1) + q];
+            zr[i][DMAX] = sZ[(jb + 16 * i) * (GPX_MAX_D + 1) + GPX_MAX_D];
+        }
+#pragma unroll
+        for (int q = 0; q < DMAX; ++q) lenr[q] = s_len[q], perr[q] = s_per[q];
+    }
+    // swizzled K* byte offsets of this thread's entries: (col, k) -> col*16 + (((k/2) ^ (col&7)) * 2) + (k&1)
+    uint32_t offK[GEN];
+#pragma unroll
+    for (int i = 0; i < GEN; ++i) {
+        const int col = jb + 16 * i;
+        offK[i] = (uint32_t)(col * W_BK + (((gk >> 1) ^ (col & 7)) << 1) + (gk & 1)) * 8u;
+    }
+    // staged training row (coords, norm, alpha) of the slice being generated, fetched one slice ahead
+    const double2 *xrow0 = reinterpret_cast<const double2 *>(xs + ((size_t)s * n_pad + gk) * XSP);
+    const double2 *xrow = xrow0;
+    double2 xr[XSP / 2];
+#pragma unroll
+    for (int q = 0; q < XSP / 2; ++q) xr[q] = __ldg(xrow + q);
+    int gi = 0, g_rb = 0, g_c = 0, g_nsl = nsl_of(0);     // next slice to generate
+    uint32_t gslot = 0;                                   // its K* ring slot
+    double macc[GEN];
+#pragma unroll
+    for (int i = 0; i < GEN; ++i) macc[i] = 0.0;
+
+    auto xr_at = [&](int q) { return (q & 1) ? xr[q >> 1].y : xr[q >> 1].x; };
+    // gen_begin: distances of this thread's GEN entries of slice gi (registers only)
+    auto gen_begin = [&](Gen &g, double &al) {
+#pragma unroll
+        for (int i = 0; i < GEN; ++i) {
+            double zq[DMAX + 1];
+#pragma unroll
+            for (int q = 0; q <= DMAX; ++q)
+                zq[q] = Z_IN_REGS ? zr[Z_IN_REGS ? i : 0][Z_IN_REGS ? q : 0]
+                                  : sZ[(jb + 16 * i) * (GPX_MAX_D + 1) + (q < DMAX ? q : GPX_MAX_D)];
             if (KIND == GPX_PERIODIC) {
                 double acc = 0.0;
-                for (int q = 0; q < d; ++q) {
-                    double df = pz[q] - __shfl_sync(0xffffffffu, xval[i], q);
-                    double sn = sin(GPX_PI * df / s_per[q]) / s_len[q];
-                    acc += sn * sn;
+#pragma unroll
+                for (int q = 0; q < DMAX; ++q) {
+                    const double pq = Z_IN_REGS ? perr[Z_IN_REGS ? q : 0] : s_per[q];
+                    const double lq = Z_IN_REGS ? lenr[Z_IN_REGS ? q : 0] : s_len[q];
+                    if (DMAX <= 2 || q < d) {
+                        double df = zq[q] - xr_at(q);
+                        double sn = sin(GPX_PI * df / pq) / lq;
+                        acc += sn * sn;
+                    }
                 }
                 g.v[i] = acc;
             } else {
                 double xz = 0.0;
-                for (int q = 0; q < d; ++q) xz = fma(pz[q], __shfl_sync(0xffffffffu, xval[i], q), xz);
-                g.v[i] = fmax((z2n - 2.0 * xz) + __shfl_sync(0xffffffffu, xval[i], d), 0.0);
-            }
-            al[i] = __shfl_sync(0xffffffffu, xval[i], d + 1);
-        }
-        // fetch the rows of the next slice (first slice of the next row block after the last)
-        const int nc = (g_c + 1 < g_nsl) ? g_c + 1 : 0;
 #pragma unroll
-        for (int i = 0; i < GEN; ++i) xval[i] = __ldg(xrow + (size_t)(nc * W_BK + i * KSTEP) * XS);
+                for (int q = 0; q < DMAX; ++q) xz = fma(zq[q], xr_at(q), xz);
+                g.v[i] = fmax((zq[DMAX] - 2.0 * xz) + xr_at(DMAX), 0.0);
+            }
+        }
+        al = xr_at(DMAX + 1);
+        // fetch the row of the next slice (first slice of the next row block after the last)
+        xrow = (g_c + 1 < g_nsl) ? xrow + (W_BK * XSP / 2) : xrow0;
+#pragma unroll
+        for (int q = 0; q < XSP / 2; ++q) xr[q] = __ldg(xrow + q);
     };
     // tma_issue (one elected thread): as soon as the stage of slice gi is released,
     // stream the W slab of that slice into it -- two slices ahead of its use
     auto tma_issue = [&]() {
         const uint32_t gst = gi % C::NST, gph = (gi / C::NST) & 1;
-        mbar_wait(bar_empty + 8 * gst, gph ^ 1);
+        mbar_wait(bar_emptyW + 8 * gst, gph ^ 1);
         if (DBG & 4) {
             mbar_arrive(bar_fullW + 8 * gst);
             return;
@@ -322,22 +372,21 @@ predict_ws_kernel(const __grid_constant__ CUtensorMap tmW, gpx_kernel_params kp,
         mbar_arrive_expect_tx(bar_fullW + 8 * gst, (uint32_t)(C::W_STAGE * sizeof(double)));
 #pragma unroll
         for (int b = 0; b < C::NBOX; ++b)
-            tma_load_3d(smem_u32(sW + (size_t)gst * C::W_STAGE + b * C::BOX_ROWS * W_BK), &tmW,
+            tma_load_3d(sW_u + (gst * C::W_STAGE + b * C::BOX_ROWS * W_BK) * 8, &tmW,
                         bar_fullW + 8 * gst, g_c * W_BK, g_rb * C::R + b * C::BOX_ROWS, s);
     };
-    // gen_end: publish the entries into the stage of slice gi
-    auto gen_end = [&](Gen &g, double (&al)[GEN]) {
-        const uint32_t gst = gi % C::NST, gph = (gi / C::NST) & 1;
-        mbar_wait(bar_empty + 8 * gst, gph ^ 1);
-        double *dst = sK + (size_t)gst * C::K_STAGE;
-        const bool do_mean = (g_rb == NRB - 1);
+    // gen_end: publish the entries into the K* slot of slice gi
+    auto gen_end = [&](Gen &g, double al) {
+        const uint32_t dst = sK_u + gslot * (C::K_STAGE * 8);
 #pragma unroll
-        for (int i = 0; i < GEN; ++i) {
-            dst[offK[i]] = g.v[i];
-            if (do_mean) macc = fma(g.v[i], al[i], macc);
+        for (int i = 0; i < GEN; ++i) sts64(dst + offK[i], g.v[i]);
+        if (g_rb == NRB - 1) {
+#pragma unroll
+            for (int i = 0; i < GEN; ++i) macc[i] = fma(g.v[i], al, macc[i]);
         }
         __syncwarp();
-        if (lane == 0) mbar_arrive(bar_fullK + 8 * gst);
+        if (lane == 0) mbar_arrive(bar_fullK + 8 * gslot);
+        if (++gslot == W_NK) gslot = 0;
         ++gi;
         if (++g_c == g_nsl) {
             g_c = 0;
@@ -348,19 +397,22 @@ predict_ws_kernel(const __grid_constant__ CUtensorMap tmW, gpx_kernel_params kp,
     // prologue: the first D slices
     for (int q = 0; q < D && gi < T; ++q) {
         Gen g;
-        double al[GEN];
+        double al;
         if (t == 0) tma_issue();
         gen_begin(g, al);
         if (!(DBG & 1)) g.template run<0, NS>(scale);
         gen_end(g, al);
     }
 
-    // lane's swizzled offset of k-pair h (k = 4 lc + 2h, +1) inside its 8-row group:
+    // lane's swizzled byte offset of k-pair h (k = 4 lc + 2h, +1) inside its 8-row group:
     // row lr, 16-byte chunk (2 lc + h) ^ lr; identical for the W slab and the K* slice
-    int offAB[2];
+    uint32_t aLane[2], bLane[2];
 #pragma unroll
-    for (int h = 0; h < 2; ++h) offAB[h] = lr * W_BK + ((((lc << 1) | h) ^ lr) << 1);
-    const int baseA = wm * 8 * W_BK, baseB = wn * 32 * W_BK;
+    for (int h = 0; h < 2; ++h) {
+        const uint32_t o = (uint32_t)(lr * W_BK + ((((lc << 1) | h) ^ lr) << 1)) * 8u;
+        aLane[h] = sW_u + (uint32_t)(wm * 8 * W_BK) * 8u + o;
+        bLane[h] = sK_u + (uint32_t)(wn * 32 * W_BK) * 8u + o;
+    }
 
     double acc[W_MF][W_NF][2];
 #pragma unroll
@@ -368,14 +420,9 @@ predict_ws_kernel(const __grid_constant__ CUtensorMap tmW, gpx_kernel_params kp,
 #pragma unroll
         for (int ni = 0; ni < W_NF; ++ni) acc[mi][ni][0] = acc[mi][ni][1] = 0.0;
 
-    uint32_t st = 0, ph = 0;          // stage / phase of the slice being multiplied
+    uint32_t st = 0, ph = 0;          // W stage / phase of the slice being multiplied
+    uint32_t slot = 0, kph = 0;       // its K* ring slot / phase
     for (int rb = 0; rb < NRB; ++rb) {
-        // Stagger the two warps of each SM sub-partition (w and w + 4) by about half a
-        // slice: they would otherwise run in lock-step (both in the non-DMMA part of the
-        // loop, then both contending for the DMMA pipe).  Offset by half a period, one
-        // warp's DMMAs cover the other's barrier / staging / generator bookkeeping.  The
-        // offset survives until the next CTA-wide barrier (end of the row block).
-        if (stagger_ns > 0 && warp >= W_WARPS / 2) __nanosleep(stagger_ns);
         const int kd0 = rb * C::R;
         const int kend = (n < kd0 + C::R) ? n : kd0 + C::R;
         const int nsl = (kend + W_BK - 1) / W_BK;
@@ -386,42 +433,45 @@ predict_ws_kernel(const __grid_constant__ CUtensorMap tmW, gpx_kernel_params kp,
         for (int c = 0; c < nsl; ++c) {
             const bool has_g = gi < T;
             Gen g;
-            double al[GEN];
+            double al = 0.0;
 #pragma unroll
-            for (int q = 0; q < GEN; ++q) g.v[q] = 0.0, al[q] = 0.0;
+            for (int q = 0; q < GEN; ++q) g.v[q] = 0.0;
             if (has_g) {
                 if (t == 0) tma_issue();
                 gen_begin(g, al);
             }
             mbar_wait(bar_fullW + 8 * st, ph);
-            mbar_wait(bar_fullK + 8 * st, ph);
-            const double *cW = sW + (size_t)st * C::W_STAGE + baseA;
-            const double *cK = sK + (size_t)st * C::K_STAGE + baseB;
+            mbar_wait(bar_fullK + 8 * slot, kph);
+            uint32_t aAddr[2], bAddr[2];
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                aAddr[h] = aLane[h] + st * (C::W_STAGE * 8);
+                bAddr[h] = bLane[h] + slot * (C::K_STAGE * 8);
+            }
             if (mi_lim >= W_MF) {
                 if (c < nsl_full) {
-                    mma_slice<0, WM, DBG>(acc, cW, cK, offAB, g, scale);
+                    mma_slice<0, WM, DBG>(acc, aAddr, bAddr, g, scale);
                 } else {
                     // diagonal block: fragment f = wm + WM*mi holds rows 8f..8f+7 and needs the
                     // slice starting at local column kl iff 8f + 7 >= kl (W is zero above its diagonal)
                     const int fa = (c * W_BK - kd0) >> 3;
                     const int mi0 = fa <= wm ? 0 : (fa - wm + WM - 1) / WM;
-                    mma_slice_from<WM, DBG>(mi0, acc, cW, cK, offAB, g, scale);
+                    mma_slice_from<WM, DBG>(mi0, acc, aAddr, bAddr, g, scale);
                 }
             } else {
                 // ragged last row block (n not a multiple of R): predicated fragments
                 if (!(DBG & 1)) g.template run<0, NS>(scale);
                 const int fa = (c * W_BK - kd0) >> 3;     // may be negative
-                int mi0 = fa <= wm ? 0 : (fa - wm + WM - 1) / WM;
+                const int mi0 = fa <= wm ? 0 : (fa - wm + WM - 1) / WM;
 #pragma unroll
                 for (int h = 0; h < 2; ++h) {
                     double2 b[W_NF];
 #pragma unroll
-                    for (int ni = 0; ni < W_NF; ++ni)
-                        b[ni] = *reinterpret_cast<const double2 *>(cK + ni * (8 * W_BK) + offAB[h]);
+                    for (int ni = 0; ni < W_NF; ++ni) b[ni] = lds128(bAddr[h] + ni * (8 * W_BK * 8));
 #pragma unroll
                     for (int mi = 0; mi < W_MF; ++mi) {
                         if (mi >= mi0 && mi < mi_lim) {
-                            const double2 a = *reinterpret_cast<const double2 *>(cW + mi * (WM * 8 * W_BK) + offAB[h]);
+                            const double2 a = lds128(aAddr[h] + mi * (WM * 8 * W_BK * 8));
 #pragma unroll
                             for (int ni = 0; ni < W_NF; ++ni) {
                                 dmma884(acc[mi][ni][0], acc[mi][ni][1], a.x, b[ni].x);
@@ -432,8 +482,9 @@ predict_ws_kernel(const __grid_constant__ CUtensorMap tmW, gpx_kernel_params kp,
                 }
             }
             __syncwarp();
-            if (lane == 0) mbar_arrive(bar_empty + 8 * st);
+            if (lane == 0) mbar_arrive(bar_emptyW + 8 * st);
             if (++st == C::NST) { st = 0; ph ^= 1; }
+            if (++slot == W_NK) { slot = 0; kph ^= 1; }
             if (has_g) gen_end(g, al);
         }
         // end of a row block: column sums of squares of its V fragments
@@ -465,7 +516,8 @@ predict_ws_kernel(const __grid_constant__ CUtensorMap tmW, gpx_kernel_params kp,
         }
         __syncthreads();
     }
-    smean[t] = macc;
+#pragma unroll
+    for (int i = 0; i < GEN; ++i) smean[i * W_THREADS + t] = macc[i];
     __syncthreads();
     if (t < C::MT) {
         const int gj = j0 + t;
@@ -476,8 +528,9 @@ predict_ws_kernel(const __grid_constant__ CUtensorMap tmW, gpx_kernel_params kp,
             if (var) var[(size_t)s * M + gj] = (kd + diag_add[s]) - colsum[t];
             if (mu) {
                 const double m0 = m_new ? m_new[(size_t)s * M + gj] : m_const;
+                // entries of candidate t were generated by the threads with jb + 16 i == t
                 double dot = 0.0;
-                for (int q = t; q < W_THREADS; q += C::MT) dot += smean[q];
+                for (int k = 0; k < 16; ++k) dot += smean[(t >> 4) * W_THREADS + (t & 15) * 16 + k];
                 mu[(size_t)s * M + gj] = m0 + dot;
             }
         }
@@ -521,7 +574,7 @@ static int make_w_tensormap(CUtensorMap *tm, const double *W, int64_t S, int64_t
     return 0;
 }
 
-template <int KIND, int WN>
+template <int KIND, int WN, int DMAX>
 static int launch_predict_ws(const gpx_kernel_params *kp, int64_t S, int64_t n, int64_t M,
                              const double *xs, const double *xnew, const double *W, int64_t ldw,
                              const double *m_new, double m_const, const double *diag_add,
@@ -529,7 +582,7 @@ static int launch_predict_ws(const gpx_kernel_params *kp, int64_t S, int64_t n, 
     using C = WCfg<WN>;
     static bool configured = false;
     if (!configured) {
-        cudaError_t e = cudaFuncSetAttribute(predict_ws_kernel<KIND, WN>,
+        cudaError_t e = cudaFuncSetAttribute(predict_ws_kernel<KIND, WN, DMAX>,
                                              cudaFuncAttributeMaxDynamicSharedMemorySize,
                                              (int)C::SMEM_BYTES);
         if (e != cudaSuccess) { set_error("gpx_predict: smem attribute failed (%d)", (int)e); return (int)e; }
@@ -540,26 +593,36 @@ static int launch_predict_ws(const gpx_kernel_params *kp, int64_t S, int64_t n, 
     if (rc) return rc;
     dim3 grid((unsigned)((M + C::MT - 1) / C::MT), (unsigned)S);
     const int n_pad = (int)((n + W_BK - 1) / W_BK * W_BK);
-    static int stagger = -1;
-    if (stagger < 0) { const char *e = getenv("GPX_STAGGER_NS"); stagger = e ? atoi(e) : W_STAGGER_NS; }
 #ifdef GPX_PREDICT_DEBUG_VARIANTS
-    if (KIND == GPX_MATERN52 && WN == 1) {
+    if (KIND == GPX_MATERN52 && WN == 1 && DMAX == 2) {
         static int dbg = -1;
         if (dbg < 0) { const char *e = getenv("GPX_PREDICT_DEBUG"); dbg = e ? atoi(e) : 0; }
 #define GPX_DBG_CASE(D)                                                                            \
         case D: {                                                                                  \
             static bool cfg = false;                                                               \
-            if (!cfg) { cudaFuncSetAttribute(predict_ws_kernel<GPX_MATERN52, 1, D>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::SMEM_BYTES); cfg = true; } \
-            predict_ws_kernel<GPX_MATERN52, 1, D><<<grid, W_THREADS, C::SMEM_BYTES, st>>>(         \
-                tm, *kp, (int)n, n_pad, (int)M, xs, xnew, m_new, m_const, diag_add, mu, var, stagger); \
+            if (!cfg) { cudaFuncSetAttribute(predict_ws_kernel<GPX_MATERN52, 1, 2, D>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::SMEM_BYTES); cfg = true; } \
+            predict_ws_kernel<GPX_MATERN52, 1, 2, D><<<grid, W_THREADS, C::SMEM_BYTES, st>>>(      \
+                tm, *kp, (int)n, n_pad, (int)M, xs, xnew, m_new, m_const, diag_add, mu, var);      \
             return 0; }
         switch (dbg) { GPX_DBG_CASE(1) GPX_DBG_CASE(2) GPX_DBG_CASE(3) default: break; }
 #undef GPX_DBG_CASE
     }
 #endif
-    predict_ws_kernel<KIND, WN><<<grid, W_THREADS, C::SMEM_BYTES, st>>>(
-        tm, *kp, (int)n, n_pad, (int)M, xs, xnew, m_new, m_const, diag_add, mu, var, stagger);
+    predict_ws_kernel<KIND, WN, DMAX><<<grid, W_THREADS, C::SMEM_BYTES, st>>>(
+        tm, *kp, (int)n, n_pad, (int)M, xs, xnew, m_new, m_const, diag_add, mu, var);
     return 0;
+}
+
+template <int KIND, int WN>
+static int launch_predict_ws_d(const gpx_kernel_params *kp, int64_t S, int64_t n, int64_t M,
+                               const double *xs, const double *xnew, const double *W, int64_t ldw,
+                               const double *m_new, double m_const, const double *diag_add,
+                               double *mu, double *var, cudaStream_t st) {
+    switch (dmax_of(kp->d)) {
+        case 2: return launch_predict_ws<KIND, WN, 2>(kp, S, n, M, xs, xnew, W, ldw, m_new, m_const, diag_add, mu, var, st);
+        case 4: return launch_predict_ws<KIND, WN, 4>(kp, S, n, M, xs, xnew, W, ldw, m_new, m_const, diag_add, mu, var, st);
+        default: return launch_predict_ws<KIND, WN, 8>(kp, S, n, M, xs, xnew, W, ldw, m_new, m_const, diag_add, mu, var, st);
+    }
 }
 
 template <int KIND>
@@ -580,8 +643,8 @@ static int dispatch_predict(const gpx_kernel_params *kp, int64_t S, int64_t n, i
     count_launches(1);
     // tall slabs amortise the K* regeneration for large n
     if (n <= 512)
-        return launch_predict_ws<KIND, 2>(kp, S, n, M, ws, xnew, W, ldw, m_new, m_const, diag_add, mu, var, st);
-    return launch_predict_ws<KIND, 1>(kp, S, n, M, ws, xnew, W, ldw, m_new, m_const, diag_add, mu, var, st);
+        return launch_predict_ws_d<KIND, 2>(kp, S, n, M, ws, xnew, W, ldw, m_new, m_const, diag_add, mu, var, st);
+    return launch_predict_ws_d<KIND, 1>(kp, S, n, M, ws, xnew, W, ldw, m_new, m_const, diag_add, mu, var, st);
 }
 
 }  // namespace gpx
@@ -589,7 +652,7 @@ static int dispatch_predict(const gpx_kernel_params *kp, int64_t S, int64_t n, i
 extern "C" size_t gpx_predict_ws_bytes(int64_t S, int64_t n, int32_t d) {
     if (n <= 128 || S <= 0) return 0;
     const size_t n_pad = (size_t)((n + gpx::W_BK - 1) / gpx::W_BK * gpx::W_BK);
-    return (size_t)S * n_pad * (size_t)(d + 2) * sizeof(double);
+    return (size_t)S * n_pad * (size_t)(gpx::dmax_of(d) + 2) * sizeof(double);
 }
 
 extern "C" int gpx_predict(const gpx_kernel_params *kp, int64_t S, int64_t n, int64_t M,
