@@ -245,7 +245,7 @@ struct KGen {
                 else if constexpr (st == 15) pl[i] = scale * pl[i];
                 else x[i] = -x[i];   // 16
             } else {
-                if constexpr (e == 0) x[i] = fmax(x[i], -1000.0);
+                if constexpr (e == 0) x[i] = x[i] < -1000.0 ? -1000.0 : x[i];
                 else if constexpr (e == 1) p[i] = fma(x[i], L2E, SHIFT);
                 else if constexpr (e == 2) { ni[i] = __double2loint(p[i]); q[i] = p[i] - SHIFT; }
                 else if constexpr (e == 3) x[i] = fma(q[i], -LN2_HI, x[i]);

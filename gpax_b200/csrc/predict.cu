@@ -102,6 +102,12 @@ __device__ __forceinline__ double2 lds128(uint32_t addr) {
     asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];\n" : "=d"(v.x), "=d"(v.y) : "r"(addr));
     return v;
 }
+// one lane of a converged warp
+__device__ __forceinline__ bool elect_one() {
+    uint32_t pred;
+    asm volatile("{\n .reg .pred p;\n elect.sync _|p, 0xffffffff;\n selp.u32 %0, 1, 0, p;\n}\n" : "=r"(pred));
+    return pred != 0;
+}
 __device__ __forceinline__ void sts64(uint32_t addr, double v) {
     asm volatile("st.shared.f64 [%0], %1;\n" ::"r"(addr), "d"(v) : "memory");
 }
@@ -351,11 +357,15 @@ predict_ws_kernel(const __grid_constant__ CUtensorMap tmW, gpx_kernel_params kp,
                 double xz = 0.0;
 #pragma unroll
                 for (int q = 0; q < DMAX; ++q) xz = fma(zq[q], xr_at(q), xz);
-                g.v[i] = fmax((zq[DMAX] - 2.0 * xz) + xr_at(DMAX), 0.0);
+                const double r2 = (zq[DMAX] - 2.0 * xz) + xr_at(DMAX);
+                g.v[i] = r2 < 0.0 ? 0.0 : r2;        // clip(0); NaN propagates like jnp.clip
             }
         }
         al = xr_at(DMAX + 1);
-        // fetch the row of the next slice (first slice of the next row block after the last)
+    };
+    // fetch the row of the next slice to generate (first slice of the next row block after
+    // the last); issued right before the DMMA block, which covers the load latency
+    auto gen_prefetch = [&]() {
         xrow = (g_c + 1 < g_nsl) ? xrow + (W_BK * XSP / 2) : xrow0;
 #pragma unroll
         for (int q = 0; q < XSP / 2; ++q) xr[q] = __ldg(xrow + q);
@@ -398,8 +408,9 @@ predict_ws_kernel(const __grid_constant__ CUtensorMap tmW, gpx_kernel_params kp,
     for (int q = 0; q < D && gi < T; ++q) {
         Gen g;
         double al;
-        if (t == 0) tma_issue();
+        if (warp == 0 && elect_one()) tma_issue();
         gen_begin(g, al);
+        gen_prefetch();
         if (!(DBG & 1)) g.template run<0, NS>(scale);
         gen_end(g, al);
     }
@@ -437,8 +448,9 @@ predict_ws_kernel(const __grid_constant__ CUtensorMap tmW, gpx_kernel_params kp,
 #pragma unroll
             for (int q = 0; q < GEN; ++q) g.v[q] = 0.0;
             if (has_g) {
-                if (t == 0) tma_issue();
+                if (warp == 0 && elect_one()) tma_issue();
                 gen_begin(g, al);
+                gen_prefetch();
             }
             mbar_wait(bar_fullW + 8 * st, ph);
             mbar_wait(bar_fullK + 8 * slot, kph);
