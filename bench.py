@@ -8,7 +8,7 @@ One "step" = one full pass of the hot path over the synthetic workload:
 Workload at N=1: BASELINE.json configs[1] ("C2": Matern-5/2, d=2, n=2048, S=1000
 posterior samples, 100x100 grid).  Multi-GPU: posterior samples are sharded over
 ranks (weak scaling: S per GPU fixed), the per-sample moments are exchanged with
-one NCCL all-to-all so each rank reduces a contiguous candidate chunk over ALL
+one NCCL all-gather so each rank reduces a contiguous candidate chunk over ALL
 samples in a fixed order, then (value, index) pairs are all-gathered.
 
   python bench.py [--gpus N --steps K --warmup W] [--impl reference]
@@ -198,7 +198,7 @@ def measure_dgemm_peak(torch, dev):
 def run_ours(args):
     import torch
     import torch.distributed as dist
-    from gpax_b200 import engine as E, _cabi
+    from gpax_b200 import engine as E, parallel as P, _cabi
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -272,31 +272,13 @@ def run_ours(args):
         E.predict(hpd, di["x"], di["x_new"], bufW, alpha, hpd.jitter, None, 1.0, True, True, mu, var, pws)
         if timed_events is not None:
             timed_events["pred1"].record()
-        if world > 1:
-            # exchange: rank r receives candidates [r*Mc, (r+1)*Mc) of every rank's samples
-            pad = Mc * world - M
-            def shard(t):
-                tt = torch.nn.functional.pad(t, (0, pad)) if pad else t
-                return tt.view(S_local, world, Mc).permute(1, 0, 2).contiguous()
-            smu, svar = shard(mu), shard(var)
-            rmu, rvar = torch.empty_like(smu), torch.empty_like(svar)
-            dist.all_to_all_single(rmu, smu)
-            dist.all_to_all_single(rvar, svar)
-            mu_all, var_all = rmu.view(world * S_local, Mc), rvar.view(world * S_local, Mc)
-            m_valid = max(0, min(Mc, M - rank * Mc))
-            mu_all, var_all = mu_all[:, :m_valid].contiguous(), var_all[:, :m_valid].contiguous()
-            off = rank * Mc
-        else:
-            mu_all, var_all, off = mu, var, 0
+        # every candidate is reduced over ALL samples on one rank, in global sample order
+        mu_all, var_all, off = P.exchange_moments(mu, var)
         o_mu, o_sd, o_acq, pv, pi = E.acq_reduce(mu_all, var_all, _cabi.ACQ_EI, 0.0, y_max,
                                                  wl.out_std + 1e-8, wl.out_mean, wl.out_std, off)
         bv, bi = E.argmax_finalize(pv, pi)
         if world > 1:
-            gv = [torch.empty_like(bv) for _ in range(world)]
-            gi = [torch.empty_like(bi) for _ in range(world)]
-            dist.all_gather(gv, bv)
-            dist.all_gather(gi, bi)
-            bv, bi = E.argmax_finalize(torch.cat(gv), torch.cat(gi))
+            bv, bi = E.argmax_finalize(*P.all_gather_pairs(bv, bi))
         return o_mu, o_sd, o_acq, bv, bi
 
     dev_inputs = {k: v.to(dev) for k, v in host_in.items()}

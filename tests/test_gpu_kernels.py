@@ -207,3 +207,106 @@ def test_argmax_ties_and_nan(cuda):
     _, _, _, pv, pi = E.acq_reduce(E._dev(mu, cuda), E._dev(var, cuda), 3)
     _, bi = E.argmax_finalize(pv, pi)
     assert int(bi.item()) == int(np.argmax(mu[0])) == 2500
+
+
+# ---------------------------------------------------------------------------
+# golden fixtures (tests/golden/*.npz, generated by tests/golden/make_golden.py)
+# ---------------------------------------------------------------------------
+import glob as _glob
+import os as _os
+
+_GOLD = _os.path.join(_os.path.dirname(__file__), "golden")
+_CASES = sorted(_os.path.basename(p)[:-4] for p in _glob.glob(_os.path.join(_GOLD, "*.npz")))
+
+
+@pytest.mark.parametrize("name", _CASES)
+def test_device_matches_golden(cuda, name):
+    """Whole hot path through the C ABI vs the committed golden vectors: per-sample
+    mean / variance / MLL to 1e-10 relative (normwise), MLL gradient to 1e-7,
+    mixture + EI / UCB argmax index bit-exact."""
+    import torch
+    from gpax_b200 import engine as E, _cabi
+    z = np.load(_os.path.join(_GOLD, name + ".npz"), allow_pickle=False)
+    hp = {k[3:]: z[k] for k in z.files if k.startswith("hp_")}
+    kind = str(z["kind"])
+    kw = {}
+    if "m_train" in z.files:
+        kw["m_train"] = z["m_train"]
+    if "y_std" in z.files:
+        kw["y_std"] = z["y_std"]
+    post = E.Posterior(kind, z["x"], z["y"], hp, device=cuda, **kw)
+    mu, var = post.predict(z["x_new"], m_new=(z["m_new"] if "m_new" in z.files else None),
+                           observation_noise=bool(z["observation_noise"]))
+    torch.cuda.synchronize()
+    assert int(post.info.abs().max()) == 0
+    assert _rel(mu.cpu().numpy(), z["mu"]) < 1e-10
+    assert _rel(var.cpu().numpy(), z["var"]) < 1e-10
+    if "y_std" not in z.files:            # the golden MLL uses k_noise (y_std is ignored during fit, gp.py:146)
+        assert _rel(post.mll.cpu().numpy(), z["mll"]) < 1e-10
+        g = post.grad()
+        torch.cuda.synchronize()
+        assert _rel(g["k_scale"].cpu().numpy(), z["grad_k_scale"][:, 0]) < 1e-7
+        assert _rel(g["k_noise"].cpu().numpy(), z["grad_k_noise"][:, 0]) < 1e-7
+        assert _rel(g["k_length"].cpu().numpy(), z["grad_k_length"]) < 1e-7
+        if "grad_k_period" in z.files:
+            assert _rel(g["k_period"].cpu().numpy(), z["grad_k_period"]) < 1e-7
+    for acq, key in ((_cabi.ACQ_EI, "argmax_ei"), (_cabi.ACQ_UCB, "argmax_ucb")):
+        _, _, o_acq, pv, pi = E.acq_reduce(mu, var, acq, 10.0, float(z["y_max"]),
+                                           float(z["out_std"]) + 1e-8, float(z["out_mean"]),
+                                           float(z["out_std"]))
+        _, bi = E.argmax_finalize(pv, pi)
+        torch.cuda.synchronize()
+        assert int(bi.item()) == int(z[key])
+
+
+# ---------------------------------------------------------------------------
+# BASELINE-size properties (no oracle at this size: identities that hold for any n)
+# ---------------------------------------------------------------------------
+@pytest.mark.parametrize("kind,n,d", [("matern52", 2048, 2), ("rbf", 1500, 1), ("periodic", 1024, 3)])
+def test_full_size_identities(cuda, kind, n, d):
+    """At x_new = x:  mean = y - D alpha  and  var = jitter + D - D^2 (K^-1)_jj  with
+    D = noise + jitter, (K^-1)_jj = ||W e_j||^2 (exact algebra of gpax/gp.py:295-301);
+    and L L^T = K on sampled entries."""
+    import torch
+    from gpax_b200 import engine as E
+    S = 2
+    x, y, xn, hp = _mk(kind, n, d, S, 4, 900 + n, period=(kind == "periodic"))
+    hp["k_noise"] = np.maximum(hp["k_noise"], 1e-3)
+    post = E.Posterior(kind, x, y, hp, device=cuda)
+    mu, var = post.predict(x)
+    torch.cuda.synchronize()
+    assert int(post.info.abs().max()) == 0
+    alpha = post.alpha.cpu().numpy()
+    W = post.W[:, :, :n]
+    kinv_diag = (torch.tril(W) ** 2).sum(1).cpu().numpy()
+    for s in range(S):
+        D = hp["k_noise"][s] + hp["k_jitter"][s]
+        assert _rel(mu[s].cpu().numpy(), y - D * alpha[s]) < 1e-9
+        ref_var = hp["k_jitter"][s] + D - D * D * kinv_diag[s]
+        assert np.max(np.abs(var[s].cpu().numpy() - ref_var)) < 1e-9 * hp["k_scale"][s]
+    # factorisation residual on a random sample of entries
+    L = torch.tril(post.L[0, :, :n])
+    rng = np.random.default_rng(0)
+    ii, jj = rng.integers(0, n, 200), rng.integers(0, n, 200)
+    per = hp["k_period"][0] if kind == "periodic" else None
+    K = O.gram(kind, x, x, hp["k_scale"][0], hp["k_length"][0], per, hp["k_noise"][0], hp["k_jitter"][0])
+    llt = (L[ii] * L[jj]).sum(1).cpu().numpy()
+    assert np.max(np.abs(llt - K[ii, jj])) < 1e-12 * hp["k_scale"][0] * 10
+
+
+def test_exp_sqrt_vec_accuracy_through_gram_free_path(cuda):
+    """The straight-line exp / sqrt of the fused predictive (common.cuh) against NumPy on a
+    case that isolates them: n = 130 (warp-specialised path), tiny W influence removed by
+    comparing k*.alpha with alpha = e_0 ... via the mean with a custom alpha is not exposed,
+    so compare the full mean against the oracle at 1e-12 on a well-conditioned problem."""
+    import torch
+    from gpax_b200 import engine as E
+    n, d, S, M = 130, 2, 3, 257
+    x, y, xn, hp = _mk("matern52", n, d, S, M, 77)
+    hp["k_noise"] = np.full(S, 0.5)          # cond(K) small -> differences are exp/sqrt ulps only
+    post = E.Posterior("matern52", x, y, hp, device=cuda)
+    mu, var = post.predict(xn)
+    torch.cuda.synchronize()
+    mu_r, var_r = O.predict_batched("matern52", x, y, xn, hp)
+    assert _rel(mu.cpu().numpy(), mu_r) < 1e-13
+    assert _rel(var.cpu().numpy(), var_r) < 1e-13
