@@ -354,9 +354,10 @@ def run_ours(args):
                     "d2h_bytes_per_step": d2h_bytes},
             "gpu_launches": int(launches),
             "clocks": clk.summary(),
-            "roofline": {"kernel": "predict_kernel (fused K* generation + W*K*^T on DMMA + column norms)",
+            "roofline": {"kernel": "predict_ws_kernel (fused K* generation + TMA-fed W*K*^T on DMMA + column norms)",
                          "bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
-                         "frac": achieved / peak if peak else None, "traffic": None,
+                         "frac": achieved / peak if peak else None,
+                         "traffic": ncu_traffic("predict_ws_kernel", S_local, n, M),
                          "peak_source": "self-measured cuBLAS DGEMM 8192^3 sustained on this GPU "
                                         "(MEASURED_PEAKS.json has no FP64 entry); burst = %.1f" % dgemm_burst,
                          "ms_per_launch": t_pred},
@@ -374,6 +375,21 @@ def run_ours(args):
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
+
+
+def ncu_traffic(kernel, S, n, M):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of ``kernel`` from the committed
+    ``ncu --set full`` capture (profiles/roofline_traffic.json), only if it was taken at this
+    launch shape; otherwise null."""
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "roofline_traffic.json")
+    try:
+        with open(path) as f:
+            for row in json.load(f):
+                if row["kernel"] == kernel and (row["S"], row["n"], row["M"]) == (S, n, M):
+                    return row["dram_bytes_read"] + row["dram_bytes_write"]
+    except (OSError, ValueError, KeyError):
+        pass
+    return None
 
 
 def _hpd_from_device(E, kind, d, di, dev):

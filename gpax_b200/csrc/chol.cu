@@ -16,17 +16,27 @@ namespace gpx {
 
 constexpr int NB = GPX_NB;
 constexpr int DLD = NB + 1;  // odd leading dimension: conflict-free row & column walks
-constexpr size_t DIAG_SMEM = (size_t)(NB * DLD + NB) * sizeof(double);
+// The diagonal block is lower triangular, so rows i and NB-1-i (i+1 and NB-i entries) share
+// one DLD-wide row of shared memory, the second stored right-to-left: 66 KB instead of
+// 132 KB, i.e. three of these latency-bound CTAs per SM instead of one.
+constexpr int FOLD_ROWS = NB / 2;
+constexpr size_t DIAG_SMEM = (size_t)(FOLD_ROWS * DLD + NB) * sizeof(double);
+
+// element (i, k), k <= i, lives at fold_base(i) + fold_step(i) * k
+__device__ __forceinline__ int fold_base(int i) {
+    return i < FOLD_ROWS ? i * DLD : (NB - 1 - i) * DLD + NB;
+}
+__device__ __forceinline__ int fold_step(int i) { return i < FOLD_ROWS ? 1 : -1; }
 
 // ---------------------------------------------------------------------------
 // diag kernel: Cholesky + inverse of one NB x NB diagonal block in shared memory
 // ---------------------------------------------------------------------------
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, 3)
 diag_kernel(int64_t n, int p, double *__restrict__ A, int64_t lda, double *__restrict__ dinv,
             int32_t *__restrict__ info) {
     extern __shared__ double sm[];
-    double *a = sm;               // [NB][DLD]
-    double *col = sm + NB * DLD;  // [NB]
+    double *a = sm;                     // folded lower triangle
+    double *col = sm + FOLD_ROWS * DLD; // [NB]
     const int64_t s = blockIdx.x;
     const int T = (int)((n + NB - 1) / NB);
     const int64_t r0 = (int64_t)p * NB;
@@ -37,31 +47,33 @@ diag_kernel(int64_t n, int p, double *__restrict__ A, int64_t lda, double *__res
     // load lower triangle; pad with identity
     for (int e = t; e < NB * NB; e += 256) {
         int i = e / NB, j = e % NB;
+        if (j > i) continue;
         double v = (i == j) ? 1.0 : 0.0;
-        if (i < nbe && j <= i) v = Ab[(int64_t)i * lda + j];
-        a[i * DLD + j] = v;
+        if (i < nbe) v = Ab[(int64_t)i * lda + j];
+        a[fold_base(i) + fold_step(i) * j] = v;
     }
     __syncthreads();
 
     // left-looking column Cholesky; thread pair (i, h) splits the k range by parity
     const int i = t >> 1, h = t & 1;
+    const int bi = fold_base(i), si = fold_step(i);
     int bad = 0;
     for (int j = 0; j < nbe; ++j) {
+        const int bj = fold_base(j), sj = fold_step(j);
         double acc = 0.0;
         if (i >= j) {
-            const double *ri = a + i * DLD, *rj = a + j * DLD;
-            for (int k = h; k < j; k += 2) acc = fma(ri[k], rj[k], acc);
+            for (int k = h; k < j; k += 2) acc = fma(a[bi + si * k], a[bj + sj * k], acc);
         }
         acc += __shfl_xor_sync(0xffffffffu, acc, 1);
-        if (i >= j && h == 0) a[i * DLD + j] -= acc;
+        if (i >= j && h == 0) a[bi + si * j] -= acc;
         __syncthreads();
-        double djj = a[j * DLD + j];
+        double djj = a[bj + sj * j];
         if (!(djj > 0.0) && bad == 0) bad = j + 1;
         double dj = sqrt(djj);
         __syncthreads();
         if (h == 0) {
-            if (i == j) a[i * DLD + j] = dj;
-            else if (i > j) a[i * DLD + j] = a[i * DLD + j] / dj;
+            if (i == j) a[bi + si * j] = dj;
+            else if (i > j) a[bi + si * j] = a[bi + si * j] / dj;
         }
         __syncthreads();
     }
@@ -72,7 +84,7 @@ diag_kernel(int64_t n, int p, double *__restrict__ A, int64_t lda, double *__res
     // write L block (zeros above the diagonal)
     for (int e = t; e < nbe * nbe; e += 256) {
         int ii = e / nbe, jj = e % nbe;
-        Ab[(int64_t)ii * lda + jj] = a[ii * DLD + jj];
+        Ab[(int64_t)ii * lda + jj] = jj <= ii ? a[fold_base(ii) + fold_step(ii) * jj] : 0.0;
     }
     __syncthreads();
 
@@ -80,26 +92,25 @@ diag_kernel(int64_t n, int p, double *__restrict__ A, int64_t lda, double *__res
     // (column j of X from the already inverted trailing block):
     //   X[j][j] = 1/L[j][j];  X[i][j] = -X[j][j] * sum_{k=j+1..i} X[i][k] L[k][j]
     for (int j = NB - 1; j >= 0; --j) {
-        if (t < NB) col[t] = a[t * DLD + j];
+        if (t < NB && t >= j) col[t] = a[fold_base(t) + fold_step(t) * j];
         __syncthreads();
         double xjj = 1.0 / col[j];
         double acc = 0.0;
         if (i > j) {
-            const double *ri = a + i * DLD;
-            for (int k = j + 1 + h; k <= i; k += 2) acc = fma(ri[k], col[k], acc);
+            for (int k = j + 1 + h; k <= i; k += 2) acc = fma(a[bi + si * k], col[k], acc);
         }
         acc += __shfl_xor_sync(0xffffffffu, acc, 1);
         __syncthreads();
         if (h == 0) {
-            if (i == j) a[i * DLD + j] = xjj;
-            else if (i > j) a[i * DLD + j] = -xjj * acc;
+            if (i == j) a[bi + si * j] = xjj;
+            else if (i > j) a[bi + si * j] = -xjj * acc;
         }
         __syncthreads();
     }
     double *Db = dinv + ((size_t)s * T + p) * NB * NB;
     for (int e = t; e < NB * NB; e += 256) {
         int ii = e / NB, jj = e % NB;
-        Db[e] = a[ii * DLD + jj];
+        Db[e] = jj <= ii ? a[fold_base(ii) + fold_step(ii) * jj] : 0.0;
     }
 }
 

@@ -38,7 +38,10 @@ def _dev(a, dev, dtype=F64):
         return None
     if isinstance(a, torch.Tensor):
         return a.to(device=dev, dtype=dtype).contiguous()
-    return torch.as_tensor(np.ascontiguousarray(a), dtype=dtype, device=dev)
+    a = np.ascontiguousarray(a)
+    if not a.flags.writeable:
+        a = a.copy()
+    return torch.as_tensor(a, dtype=dtype, device=dev)
 
 
 def even(n):
@@ -169,6 +172,8 @@ def predict(hpd: HyperParams, x, x_new, W, alpha, diag_add, m_new=None, m_const=
     dev = x.device
     if ws is None:
         ws = predict_ws_alloc(S, n, hpd.d, dev)
+    if m_new is not None and tuple(m_new.shape) != (S, M):
+        raise ValueError(f"m_new must have shape (S, M) = ({S}, {M}), got {tuple(m_new.shape)}")
     if want_mu and mu is None:
         mu = torch.empty((S, M), dtype=F64, device=dev)
     if want_var and var is None:

@@ -272,8 +272,10 @@ def predict_batched(kind, x, y, x_new, hp, m_train=None, m_new=None, y_std=None,
 
 
 def median_hp(hp):
-    """``fast=True`` (gpax/gp.py:539-542): per-parameter median over S, keepdims."""
-    return {k: (None if v is None else np.median(v, axis=0, keepdims=True))
+    """``fast=True`` (gpax/gp.py:345-349,539-542): ``jnp.median(value, keepdims=True)``
+    has no axis argument, so a plated ``[S, d]`` parameter collapses to ONE median
+    over all S*d entries (shape ``(1, 1)``), not to a per-dimension median."""
+    return {k: (None if v is None else np.median(v, keepdims=True))
             for k, v in hp.items()}
 
 

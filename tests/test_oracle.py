@@ -211,7 +211,7 @@ def test_mixture_moments_and_median():
     np.testing.assert_array_equal(m1, mu[0])
     hp = {"k_scale": rng.uniform(1, 2, 9), "k_length": rng.uniform(1, 2, (9, 2)), "k_period": None}
     med = O.median_hp(hp)
-    assert med["k_scale"].shape == (1,) and med["k_length"].shape == (1, 2) and med["k_period"] is None
+    assert med["k_scale"].shape == (1,) and med["k_length"].shape == (1, 1) and med["k_period"] is None
 
 
 def test_transforms_match_reference_round_trips():
