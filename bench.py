@@ -367,7 +367,7 @@ def run_ours(args):
             "argmax": {"index": int(res[4].item()), "value": float(res[3].item())},
         }
         if not args.no_cpu_baseline and world == 1:
-            ns = args.cpu_samples or 8
+            ns = args.cpu_samples or 24
             v, dt = cpu_baseline_run(wl, min(ns, wl.S))
             line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": host_threads(), "kind": "port",
                                     "sample": f"{min(ns, wl.S)} of {wl.S} posterior samples x all {M} "

@@ -364,3 +364,79 @@ def test_c4_single_large_matrix_mll_and_grad(cuda):
     fd = (mll_at(+1) - mll_at(-1)) / (2 * h)
     an = float(np.sum(gvec * t0 * dirn))            # d/d log(theta) = theta * d/d theta
     assert abs(fd - an) / max(1.0, abs(an)) < 1e-5
+
+
+def test_c1_full_size_vs_oracle(cuda):
+    """BASELINE config C1 at full size (RBF, d=1, n=64, S=500, M=200): the oracle finishes
+    it in seconds, so this is a direct comparison -- per-sample mean/variance and MLL at
+    1e-10 (normwise), mixture + EI/UCB argmax index bit-exact."""
+    import torch
+    from gpax_b200 import engine as E, synthetic as syn, _cabi
+    wl = syn.config1()
+    post = E.Posterior(wl.kind, wl.x, wl.y, wl.hp, device=cuda)
+    mu, var = post.predict(wl.x_new)
+    torch.cuda.synchronize()
+    assert int(post.info.abs().max()) == 0
+    mu_o, var_o = O.predict_batched(wl.kind, wl.x, wl.y, wl.x_new, wl.hp, diag_only=True)
+    assert _rel(mu.cpu().numpy(), mu_o) < 1e-10
+    assert _rel(var.cpu().numpy(), var_o) < 1e-10
+    mll_o = np.array([O.mll(wl.kind, wl.x, wl.y, np.ones(wl.n), wl.hp["k_scale"][s], wl.hp["k_length"][s],
+                            wl.hp["k_noise"][s], wl.hp["k_jitter"][s]) for s in range(wl.S)])
+    assert np.max(np.abs(post.mll.cpu().numpy() - mll_o) / np.abs(mll_o)) < 1e-10
+    mbar, vbar = O.mixture_moments(mu_o, var_o)
+    mu_u, sd_u = mbar * (wl.out_std + 1e-8) + wl.out_mean, np.sqrt(vbar) * wl.out_std
+    for acq, beta in ((_cabi.ACQ_EI, 0.0), (_cabi.ACQ_UCB, 10.0), (_cabi.ACQ_UE, 0.0)):
+        ref = O.acquisition(acq, mu_u, sd_u, beta, float(wl.y_raw.max()))
+        _, _, o_acq, pv, pi = E.acq_reduce(mu, var, acq, beta, float(wl.y_raw.max()),
+                                           wl.out_std + 1e-8, wl.out_mean, wl.out_std)
+        _, bi = E.argmax_finalize(pv, pi)
+        torch.cuda.synchronize()
+        assert _rel(o_acq.cpu().numpy(), ref) < 1e-8
+        assert int(bi.item()) == O.first_argmax(ref)
+
+
+def test_c3_full_size_acquisition_sweep(cuda):
+    """BASELINE config C3 at full size (M = 10^6 candidates, S = 2000, n = 64), swept in four
+    candidate chunks with ``m_offset`` exactly as the M-sharded multi-GPU layout does
+    (SURVEY.md section 8e).  Checks: (i) a random subset of 400 candidates against the oracle
+    over ALL 2000 samples (mean/sd of the mixture at 1e-9, EI at 1e-7); (ii) the global
+    winner assembled from the chunk winners equals the first maximum of the full device
+    acquisition array (index bit-exact), for EI and UCB."""
+    import torch
+    from gpax_b200 import engine as E, synthetic as syn, _cabi
+    wl = syn.config3()
+    S, M = wl.S, wl.M
+    post = E.Posterior(wl.kind, wl.x, wl.y, wl.hp, device=cuda)
+    assert int(post.info.abs().max()) == 0
+    xn = E._dev(wl.x_new, cuda)
+    y_max = float(wl.y_raw.max())
+    a, b, c = wl.out_std + 1e-8, wl.out_mean, wl.out_std
+    chunks = 4
+    mc = M // chunks
+    out = {k: {"mu": [], "sd": [], "acq": [], "pv": [], "pi": []} for k in ("ei", "ucb")}
+    for ci in range(chunks):
+        mu, var = post.predict(xn[ci * mc:(ci + 1) * mc])
+        for name, acq, beta in (("ei", _cabi.ACQ_EI, 0.0), ("ucb", _cabi.ACQ_UCB, 10.0)):
+            o_mu, o_sd, o_acq, pv, pi = E.acq_reduce(mu, var, acq, beta, y_max, a, b, c, m_offset=ci * mc)
+            for k, v in zip(("mu", "sd", "acq", "pv", "pi"), (o_mu, o_sd, o_acq, pv, pi)):
+                out[name][k].append(v)
+        del mu, var
+    torch.cuda.synchronize()
+    rng = np.random.default_rng(0)
+    sub = np.sort(rng.choice(M, 400, replace=False))
+    mu_o, var_o = O.predict_batched(wl.kind, wl.x, wl.y, wl.x_new[sub], wl.hp, diag_only=True)
+    mbar, vbar = O.mixture_moments(mu_o, var_o)
+    mu_u, sd_u = mbar * a + b, np.sqrt(vbar) * c
+    for name, acq, beta in (("ei", _cabi.ACQ_EI, 0.0), ("ucb", _cabi.ACQ_UCB, 10.0)):
+        o = out[name]
+        full_mu = torch.cat(o["mu"]).cpu().numpy()
+        full_sd = torch.cat(o["sd"]).cpu().numpy()
+        full_acq = torch.cat(o["acq"]).cpu().numpy()
+        assert _rel(full_mu[sub], mu_u) < 1e-9
+        assert _rel(full_sd[sub], sd_u) < 1e-9
+        ref = O.acquisition(acq, mu_u, sd_u, beta, y_max)
+        assert _rel(full_acq[sub], ref) < 1e-7
+        bv, bi = E.argmax_finalize(torch.cat(o["pv"]), torch.cat(o["pi"]))
+        torch.cuda.synchronize()
+        assert int(bi.item()) == int(np.argmax(full_acq))
+        assert float(bv.item()) == float(full_acq[int(bi.item())])
