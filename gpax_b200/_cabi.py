@@ -52,7 +52,8 @@ SIGNATURES = {
     "gpx_dinv_bytes": (_sz, [_i64, _i64]),
     "gpx_potrf_batched": (C.c_int, [_i64, _i64, _ptr, _i64, _ptr, _ptr, _ptr]),
     "gpx_trtri_batched": (C.c_int, [_i64, _i64, _ptr, _i64, _ptr, _ptr, _i64, _ptr]),
-    "gpx_mll": (C.c_int, [_i64, _i64, _ptr, _i64, _ptr, _ptr, _i64, _ptr, _ptr, _ptr]),
+    "gpx_mll_ws_bytes": (_sz, [_i64, _i64]),
+    "gpx_mll": (C.c_int, [_i64, _i64, _ptr, _i64, _ptr, _ptr, _i64, _ptr, _ptr, _ptr, _ptr]),
     "gpx_mll_grad_ws_bytes": (_sz, [_i64, _i64, _i32]),
     "gpx_mll_grad": (C.c_int, [_kp, _i64, _i64, _ptr, _ptr, _i64, _ptr, _ptr, _ptr, _ptr, _ptr,
                                _ptr, _ptr]),
@@ -70,7 +71,7 @@ for _name, (_res, _args) in SIGNATURES.items():
     _fn.restype = _res
     _fn.argtypes = _args
 
-ABI_VERSION = 2
+ABI_VERSION = 3
 if lib.gpx_abi_version() != ABI_VERSION:
     raise ImportError("libgpax_b200.so ABI version mismatch")
 

@@ -62,7 +62,17 @@ diag_kernel(int64_t n, int p, double *__restrict__ A, int64_t lda, double *__res
         const int bj = fold_base(j), sj = fold_step(j);
         double acc = 0.0;
         if (i >= j) {
-            for (int k = h; k < j; k += 2) acc = fma(a[bi + si * k], a[bj + sj * k], acc);
+            // four independent chains: the loop is shared-memory-latency bound
+            double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
+            int k = h;
+            for (; k + 6 < j; k += 8) {
+                a0 = fma(a[bi + si * k], a[bj + sj * k], a0);
+                a1 = fma(a[bi + si * (k + 2)], a[bj + sj * (k + 2)], a1);
+                a2 = fma(a[bi + si * (k + 4)], a[bj + sj * (k + 4)], a2);
+                a3 = fma(a[bi + si * (k + 6)], a[bj + sj * (k + 6)], a3);
+            }
+            for (; k < j; k += 2) a0 = fma(a[bi + si * k], a[bj + sj * k], a0);
+            acc = (a0 + a1) + (a2 + a3);
         }
         acc += __shfl_xor_sync(0xffffffffu, acc, 1);
         if (i >= j && h == 0) a[bi + si * j] -= acc;
@@ -97,7 +107,16 @@ diag_kernel(int64_t n, int p, double *__restrict__ A, int64_t lda, double *__res
         double xjj = 1.0 / col[j];
         double acc = 0.0;
         if (i > j) {
-            for (int k = j + 1 + h; k <= i; k += 2) acc = fma(a[bi + si * k], col[k], acc);
+            double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
+            int k = j + 1 + h;
+            for (; k + 6 <= i; k += 8) {
+                a0 = fma(a[bi + si * k], col[k], a0);
+                a1 = fma(a[bi + si * (k + 2)], col[k + 2], a1);
+                a2 = fma(a[bi + si * (k + 4)], col[k + 4], a2);
+                a3 = fma(a[bi + si * (k + 6)], col[k + 6], a3);
+            }
+            for (; k <= i; k += 2) a0 = fma(a[bi + si * k], col[k], a0);
+            acc = (a0 + a1) + (a2 + a3);
         }
         acc += __shfl_xor_sync(0xffffffffu, acc, 1);
         __syncthreads();

@@ -131,15 +131,17 @@ def trtri(L, n, dinv, W=None):
     return W
 
 
-def mll(L, n, dinv, resid, want_alpha=True):
+def mll(L, n, dinv, resid, want_alpha=True, ws=None):
     """resid: [n] (shared) or [S, n]."""
     S, _, ldl = L.shape
     dev = L.device
+    if ws is None:
+        ws = torch.empty(max(1, lib.gpx_mll_ws_bytes(S, n) // 8), dtype=F64, device=dev)
     stride = 0 if resid.dim() == 1 else n
     alpha = torch.empty((S, n), dtype=F64, device=dev) if want_alpha else None
     val = torch.empty(S, dtype=F64, device=dev)
     check(lib.gpx_mll(S, n, _ptr(L), ldl, _ptr(dinv), _ptr(resid), stride, _ptr(alpha),
-                      _ptr(val), _stream()), "gpx_mll")
+                      _ptr(val), _ptr(ws), _stream()), "gpx_mll")
     return val, alpha
 
 

@@ -37,7 +37,7 @@
 extern "C" {
 #endif
 
-#define GPX_ABI_VERSION 2
+#define GPX_ABI_VERSION 3
 
 /* covariance families: gpax/kernels.py:110 (RBF), :129 (Matern nu=5/2), :150 (Periodic) */
 enum { GPX_RBF = 0, GPX_MATERN52 = 1, GPX_PERIODIC = 2 };
@@ -109,10 +109,15 @@ int gpx_trtri_batched(int64_t S, int64_t n, const double *L, int64_t ldl,
  * replaces gpax/gp.py:147-151 (log density) and cho_solve(K, y - m) gpax/gp.py:300.
  *   resid [.., n] with sample stride resid_stride (0: shared by all samples).
  *   alpha [S, n] out (nullable); mll [S] out (nullable).
+ *   ws: gpx_mll_ws_bytes(S, n) bytes, or NULL.  With a workspace, few large
+ *   matrices (S < 256, n >= 512; e.g. BASELINE config n = 16384, S = 1) are solved
+ *   by a multi-CTA blocked substitution; without one every sample is solved by a
+ *   single CTA, which needs n <= ~28k.
  */
+size_t gpx_mll_ws_bytes(int64_t S, int64_t n);
 int gpx_mll(int64_t S, int64_t n, const double *L, int64_t ldl, const double *dinv,
             const double *resid, int64_t resid_stride,
-            double *alpha, double *mll, void *stream);
+            double *alpha, double *mll, void *ws, void *stream);
 
 /* gpx_mll_grad: gradient of the log density above w.r.t. the kernel
  * hyper-parameters, 0.5 tr((alpha alpha^T - K^-1) dK/dtheta), with K^-1 = W^T W

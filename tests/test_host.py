@@ -46,6 +46,7 @@ def test_cabi_size_queries_and_argument_errors():
     assert lib.gpx_predict_ws_bytes(5, 1000, 3) == 5 * 1008 * 6 * 8
     assert lib.gpx_acq_parts(1000) == 4
     assert lib.gpx_mll_grad_ws_bytes(2, 300, 2) > 0
+    assert lib.gpx_mll_ws_bytes(3, 300) == 2 * 3 * 384 * 8
     kp = _cabi.KernelParams(7, 2, 1, 0, 0, 0, 0)        # invalid kind
     rc = lib.gpx_gram(C.byref(kp), 1, 4, 4, None, None, None, 0, 0, None, 0, 0, None, 4, None)
     assert rc == -1
