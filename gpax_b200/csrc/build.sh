@@ -9,6 +9,11 @@ FLAGS=(-gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -std=c++17 -Xcompil
 pids=()
 for f in api gram chol mll predict acq mll_grad; do
   [ -f "$here/$f.cu" ] || continue
+  # incremental: skip objects newer than their source, every header and this script
+  if [ -z "${GPX_REBUILD:-}" ] && [ -f "$here/obj/$f.o" ] && \
+     [ -z "$(find "$here" "$here/../../include" -maxdepth 1 \( -name "$f.cu" -o -name '*.cuh' -o -name '*.h' -o -name build.sh \) -newer "$here/obj/$f.o" | head -1)" ]; then
+    continue
+  fi
   extra=()
   # acquisition arithmetic must match NumPy's un-fused mul/add bit for bit
   [ "$f" = acq ] && extra=(-fmad=false)

@@ -136,7 +136,8 @@ diag_kernel(int64_t n, int p, double *__restrict__ A, int64_t lda, double *__res
 // ---------------------------------------------------------------------------
 // tile kernels (one CTA = one 128x128 tile; blockIdx.y = sample)
 // ---------------------------------------------------------------------------
-enum { OP_SYRK_LEFT = 0, OP_SYRK_RIGHT = 1, OP_TRSM = 2, OP_TRTRI_ACC = 3, OP_TRTRI_FIN = 4 };
+enum { OP_SYRK_LEFT = 0, OP_SYRK_RIGHT = 1, OP_TRSM = 2, OP_TRTRI_ACC = 3, OP_TRTRI_FIN = 4,
+       OP_TRTRI_RIGHT = 5 };
 
 template <int OP>
 __global__ void __launch_bounds__(T_THREADS, 1)
@@ -159,7 +160,7 @@ tile_kernel(int64_t n, int p, double *__restrict__ A, int64_t lda, const double 
         Operand a{As, lda, i * NB, 0, n, n};
         Operand b{As, lda, (int64_t)p * NB, 0, n, n};
         tile_gemm<false>(smem, a, b, (int64_t)p * NB, acc);
-        tile_store(As, lda, i * NB, (int64_t)p * NB, n, n, -1.0, true, acc);
+        tile_store<false>(As, lda, i * NB, (int64_t)p * NB, n, n, -1.0, true, acc);
     } else if (OP == OP_SYRK_RIGHT) {
         // tile (i, j), p < j <= i < T from a triangular enumeration; K = block p
         const int64_t id = blockIdx.x;
@@ -171,7 +172,7 @@ tile_kernel(int64_t n, int p, double *__restrict__ A, int64_t lda, const double 
         Operand a{As, lda, i * NB, (int64_t)p * NB, n, n};
         Operand b{As, lda, j * NB, (int64_t)p * NB, n, n};
         tile_gemm<false>(smem, a, b, NB, acc);
-        tile_store(As, lda, i * NB, j * NB, n, n, -1.0, true, acc);
+        tile_store<false>(As, lda, i * NB, j * NB, n, n, -1.0, true, acc);
     } else if (OP == OP_TRSM) {
         // tile (i, p), i = p + 1 + blockIdx.x:  A(i,p) <- A(i,p) * Dinv(p)^T
         const int64_t i = p + 1 + blockIdx.x;
@@ -179,14 +180,22 @@ tile_kernel(int64_t n, int p, double *__restrict__ A, int64_t lda, const double 
         Operand a{As, lda, i * NB, (int64_t)p * NB, n, n};
         Operand b{D, NB, 0, 0, NB, NB};
         tile_gemm<false>(smem, a, b, NB, acc);
-        tile_store(As, lda, i * NB, (int64_t)p * NB, n, n, 1.0, false, acc);
+        tile_store<false>(As, lda, i * NB, (int64_t)p * NB, n, n, 1.0, false, acc);
     } else if (OP == OP_TRTRI_ACC) {
         // W(p, j) = sum_{k=j..p-1} L(p,k) W(k,j), j = blockIdx.x  (A is W here)
         const int64_t j = blockIdx.x;
         Operand a{Ls, ldl, (int64_t)p * NB, j * NB, n, n};
         Operand b{As, lda, j * NB, j * NB, n, n};
         tile_gemm<true>(smem, a, b, (int64_t)(p - j) * NB, acc);
-        tile_store(As, lda, (int64_t)p * NB, j * NB, n, n, 1.0, false, acc);
+        tile_store<true>(As, lda, (int64_t)p * NB, j * NB, n, n, 1.0, false, acc);
+    } else if (OP == OP_TRTRI_RIGHT) {
+        // right-looking step p: W(i, j) (+)= L(i,p) W(p,j) for p < i < T, 0 <= j <= p
+        // (blockIdx.x = (i - p - 1) * (p + 1) + j; tile (i, p) receives its first term here)
+        const int64_t i = p + 1 + blockIdx.x / (p + 1), j = blockIdx.x % (p + 1);
+        Operand a{Ls, ldl, i * NB, (int64_t)p * NB, n, n};
+        Operand b{As, lda, (int64_t)p * NB, j * NB, n, n};
+        tile_gemm<true>(smem, a, b, NB, acc);
+        tile_store<true>(As, lda, i * NB, j * NB, n, n, 1.0, j != p, acc);
     } else {
         // W(p, j) <- -Dinv(p) * W(p, j), j = blockIdx.x
         const int64_t j = blockIdx.x;
@@ -194,7 +203,7 @@ tile_kernel(int64_t n, int p, double *__restrict__ A, int64_t lda, const double 
         Operand a{D, NB, 0, 0, NB, NB};
         Operand b{As, lda, (int64_t)p * NB, j * NB, n, n};
         tile_gemm<true>(smem, a, b, NB, acc);
-        tile_store(As, lda, (int64_t)p * NB, j * NB, n, n, -1.0, false, acc);
+        tile_store<true>(As, lda, (int64_t)p * NB, j * NB, n, n, -1.0, false, acc);
     }
 }
 
@@ -227,6 +236,7 @@ static int set_attrs_once() {
     GPX_SET(tile_kernel<OP_TRSM>, T_SMEM_BYTES);
     GPX_SET(tile_kernel<OP_TRTRI_ACC>, T_SMEM_BYTES);
     GPX_SET(tile_kernel<OP_TRTRI_FIN>, T_SMEM_BYTES);
+    GPX_SET(tile_kernel<OP_TRTRI_RIGHT>, T_SMEM_BYTES);
 #undef GPX_SET
     done = 1;
     return 0;
@@ -299,11 +309,26 @@ extern "C" int gpx_trtri_batched(int64_t S, int64_t n, const double *L, int64_t 
         trtri_diag_copy_kernel<<<g, 256, 0, st>>>(n, dinv, W, ldw);
         count_launches(1);
     }
-    for (int p = 1; p < T; ++p) {
-        dim3 g((unsigned)p, (unsigned)S);
-        tile_kernel<OP_TRTRI_ACC><<<g, T_THREADS, T_SMEM_BYTES, st>>>(n, p, W, ldw, L, ldl, dinv);
-        tile_kernel<OP_TRTRI_FIN><<<g, T_THREADS, T_SMEM_BYTES, st>>>(n, p, W, ldw, L, ldl, dinv);
-        count_launches(2);
+    // block row p of W:  W(p,j) = -Dinv(p) * sum_{k=j..p-1} L(p,k) W(k,j).  LEFT-looking
+    // (deep-K sum per tile, p tiles per launch) when the batch fills the machine;
+    // RIGHT-looking (rank-NB update of every row below p, (T-p-1)(p+1) tiles per launch)
+    // for few large matrices, where a block row alone is less than one wave.
+    const bool left = (S * (int64_t)((T + 1) / 2) >= 296);
+    for (int p = 0; p < T; ++p) {
+        if (p > 0) {
+            dim3 g((unsigned)p, (unsigned)S);
+            if (left) {
+                tile_kernel<OP_TRTRI_ACC><<<g, T_THREADS, T_SMEM_BYTES, st>>>(n, p, W, ldw, L, ldl, dinv);
+                count_launches(1);
+            }
+            tile_kernel<OP_TRTRI_FIN><<<g, T_THREADS, T_SMEM_BYTES, st>>>(n, p, W, ldw, L, ldl, dinv);
+            count_launches(1);
+        }
+        if (!left && p + 1 < T) {
+            dim3 g((unsigned)((int64_t)(T - p - 1) * (p + 1)), (unsigned)S);
+            tile_kernel<OP_TRTRI_RIGHT><<<g, T_THREADS, T_SMEM_BYTES, st>>>(n, p, W, ldw, L, ldl, dinv);
+            count_launches(1);
+        }
     }
     GPX_LAUNCH_CHECK();
     return 0;

@@ -111,13 +111,13 @@ mll_grad_tile_kernel(gpx_kernel_params kp, int64_t n, const double *__restrict__
 
 #pragma unroll
     for (int mi = 0; mi < T_MF; ++mi) {
-        const int64_t gi = i0 + wm * 64 + mi * 8 + lr;
+        const int64_t gi = i0 + tile_row<true>(wm, mi, lr);
         const double ai = gi < n ? al[gi] : 0.0;
 #pragma unroll
         for (int ni = 0; ni < T_NF; ++ni) {
 #pragma unroll
             for (int e = 0; e < 2; ++e) {
-                const int64_t gj = j0 + wn * 32 + ni * 8 + lc * 2 + e;
+                const int64_t gj = j0 + tile_col<true>(wn, ni, lc, e);
                 if (gi < n && gj < n) {
                     const double g = wgt * (ai * al[gj] - acc[mi][ni][e]);
                     grad_elem(kp, x, s_len, s_per, scale, gi, gj, g, part);
