@@ -64,6 +64,11 @@ SIGNATURES = {
     "gpx_acq_reduce": (C.c_int, [_i64, _i64, _ptr, _ptr, _i32, _dbl, _dbl, _dbl, _dbl, _dbl,
                                  _i64, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr]),
     "gpx_argmax_finalize": (C.c_int, [_i64, _ptr, _ptr, _ptr, _ptr, _ptr]),
+    "gpx_predict_acq_tile": (_i64, [_i64, _i64]),
+    "gpx_predict_acq_ws_bytes": (_sz, [_i64, _i64, _i32, _i64]),
+    "gpx_predict_acq": (C.c_int, [_kp, _i64, _i64, _i64, _ptr, _ptr, _ptr, _i64, _ptr, _ptr, _dbl,
+                                  _ptr, _i32, _dbl, _dbl, _dbl, _dbl, _dbl, _i64, _i64, _ptr, _ptr,
+                                  _ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr]),
 }
 
 for _name, (_res, _args) in SIGNATURES.items():
@@ -71,7 +76,7 @@ for _name, (_res, _args) in SIGNATURES.items():
     _fn.restype = _res
     _fn.argtypes = _args
 
-ABI_VERSION = 3
+ABI_VERSION = 4
 if lib.gpx_abi_version() != ABI_VERSION:
     raise ImportError("libgpax_b200.so ABI version mismatch")
 

@@ -14,6 +14,7 @@
 namespace gpx {
 
 constexpr int A_THREADS = 256;
+constexpr int A_CW = 32;        // candidates per partial-winner slot (gpx_acq_parts)
 
 struct Best {
     double v;
@@ -86,7 +87,6 @@ acq_reduce_kernel(int64_t S, int64_t M, const double *__restrict__ mu,
                   double *__restrict__ out_mu, double *__restrict__ out_sd,
                   double *__restrict__ out_acq, double *__restrict__ part_val,
                   int64_t *__restrict__ part_idx) {
-    __shared__ Best sbuf[A_THREADS / 32];
     const int64_t j = (int64_t)blockIdx.x * A_THREADS + threadIdx.x;
     Best mine;
     mine.v = -INFINITY;
@@ -129,10 +129,114 @@ acq_reduce_kernel(int64_t S, int64_t M, const double *__restrict__ mu,
         mine.v = val;
         mine.i = m_offset + j;
     }
-    Best b = block_best(mine, sbuf);
-    if (threadIdx.x == 0) {
-        part_val[blockIdx.x] = b.v;
-        part_idx[blockIdx.x] = b.i;
+    // one partial winner per A_CW = 32 candidates (gpx_acq_parts): each warp owns one slot
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        Best r = best_shfl(mine, o);
+        if (better(r, mine)) mine = r;
+    }
+    const int64_t slot = (int64_t)blockIdx.x * (A_THREADS / A_CW) + (threadIdx.x >> 5);
+    if ((threadIdx.x & 31) == 0 && slot * A_CW < M) {
+        part_val[slot] = mine.v;
+        part_idx[slot] = mine.i;
+    }
+}
+
+// Narrow variant for small / tiled M (gpx_predict_acq tiles, C2's 10^4-point grid): one CTA
+// owns only A_CW = 32 candidates, so 8x more CTAs exist for the same M.  All 8 warps fetch
+// rows (4 samples each per chunk, mu and var -> 8 loads in flight per thread) into a
+// double-buffered shared tile; warp 0 alone walks the chunk in the fixed order
+// s = 0..S-1, so the sums are bit-identical to the wide kernel above.
+constexpr int A_ROWS = 32;
+__global__ void __launch_bounds__(A_THREADS)
+acq_reduce_narrow_kernel(int64_t S, int64_t M, const double *__restrict__ mu,
+                         const double *__restrict__ var, int acq, double coef, double y_max,
+                         double mu_scale, double mu_shift, double sd_scale, int64_t m_offset,
+                         double *__restrict__ out_mu, double *__restrict__ out_sd,
+                         double *__restrict__ out_acq, double *__restrict__ part_val,
+                         int64_t *__restrict__ part_idx) {
+    __shared__ double s_mu[2][A_ROWS][A_CW];
+    __shared__ double s_var[2][A_ROWS][A_CW];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int64_t j = (int64_t)blockIdx.x * A_CW + lane;
+    const bool live = j < M;
+    constexpr int RPW = A_ROWS / (A_THREADS / 32);   // rows per warp per chunk
+    double rm[RPW], rv[RPW];
+    auto fetch = [&](int64_t s0) {
+#pragma unroll
+        for (int q = 0; q < RPW; ++q) {
+            const int64_t s = s0 + warp * RPW + q;
+            const bool ok = live && s < S;
+            rm[q] = ok ? mu[s * M + j] : 0.0;
+            rv[q] = ok ? var[s * M + j] : 0.0;
+        }
+    };
+    auto stash = [&](int buf) {
+#pragma unroll
+        for (int q = 0; q < RPW; ++q) {
+            s_mu[buf][warp * RPW + q][lane] = rm[q];
+            s_var[buf][warp * RPW + q][lane] = rv[q];
+        }
+    };
+    double a = 0.0, b = 0.0;
+    fetch(0);
+    stash(0);
+    __syncthreads();
+    int buf = 0;
+    for (int64_t s0 = 0; s0 < S; s0 += A_ROWS) {
+        const bool more = s0 + A_ROWS < S;
+        if (more) fetch(s0 + A_ROWS);           // next chunk's loads fly during the walk below
+        if (warp == 0) {
+            const int rows = (int)((S - s0 < A_ROWS) ? (S - s0) : A_ROWS);
+            if (rows == A_ROWS) {
+#pragma unroll 8
+                for (int r = 0; r < A_ROWS; ++r) {
+                    const double m1 = s_mu[buf][r][lane], v1 = s_var[buf][r][lane];
+                    a = a + m1;
+                    b = b + (v1 + m1 * m1);
+                }
+            } else {
+                for (int r = 0; r < rows; ++r) {
+                    const double m1 = s_mu[buf][r][lane], v1 = s_var[buf][r][lane];
+                    a = a + m1;
+                    b = b + (v1 + m1 * m1);
+                }
+            }
+        }
+        if (more) stash(buf ^ 1);
+        __syncthreads();
+        buf ^= 1;
+    }
+    if (warp != 0) return;
+    Best mine;
+    mine.v = -INFINITY;
+    mine.i = INT64_MAX;
+    if (live) {
+        double mbar, vbar;
+        if (S == 1) {
+            mbar = mu[j];                        // S == 1: analytic pass-through (the `fast` path),
+            vbar = var[j];                       // not (var + mu*mu) - mu*mu
+        } else {
+            mbar = a / (double)S;
+            vbar = b / (double)S - mbar * mbar;
+        }
+        const double mu_u = mbar * mu_scale + mu_shift;
+        const double sd_u = sqrt(vbar) * sd_scale;
+        const double val = acq_value(acq, mu_u, sd_u, coef, y_max);
+        if (out_mu) out_mu[j] = mu_u;
+        if (out_sd) out_sd[j] = sd_u;
+        if (out_acq) out_acq[j] = val;
+        mine.v = val;
+        mine.i = m_offset + j;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        Best r = best_shfl(mine, o);
+        if (better(r, mine)) mine = r;
+    }
+    if (lane == 0) {
+        part_val[blockIdx.x] = mine.v;
+        part_idx[blockIdx.x] = mine.i;
     }
 }
 
@@ -159,7 +263,7 @@ argmax_finalize_kernel(int64_t P, const double *__restrict__ part_val,
 
 }  // namespace gpx
 
-extern "C" int64_t gpx_acq_parts(int64_t M) { return (M + gpx::A_THREADS - 1) / gpx::A_THREADS; }
+extern "C" int64_t gpx_acq_parts(int64_t M) { return (M + gpx::A_CW - 1) / gpx::A_CW; }
 
 extern "C" int gpx_acq_reduce(int64_t S, int64_t M, const double *mu, const double *var,
                               int32_t acq, double beta, double y_max, double mu_scale,
@@ -182,10 +286,22 @@ extern "C" int gpx_acq_reduce(int64_t S, int64_t M, const double *mu, const doub
         else if (beta == 0.0) acq = GPX_ACQ_MEAN;
         else coef = sqrt(beta + 1e-12);
     }
-    unsigned grid = (unsigned)gpx_acq_parts(M);
-    acq_reduce_kernel<<<grid, A_THREADS, 0, (cudaStream_t)stream>>>(
-        S, M, mu, var, acq, coef, y_max, mu_scale, mu_shift, sd_scale, m_offset, out_mu, out_sd,
-        out_acq, part_val, part_idx);
+    // wide kernel (256 candidates per CTA) once it fills the machine several times over,
+    // narrow kernel (32 per CTA) below that; GPX_ACQ_VARIANT=1|2 forces one (profiling only)
+    static int forced = -1;
+    if (forced < 0) { const char *e = getenv("GPX_ACQ_VARIANT"); forced = e ? atoi(e) : 0; }
+    const bool wide = forced == 1 || (forced != 2 && M >= (int64_t)A_THREADS * 148 * 8);
+    if (wide) {
+        unsigned grid = (unsigned)((M + A_THREADS - 1) / A_THREADS);
+        acq_reduce_kernel<<<grid, A_THREADS, 0, (cudaStream_t)stream>>>(
+            S, M, mu, var, acq, coef, y_max, mu_scale, mu_shift, sd_scale, m_offset, out_mu,
+            out_sd, out_acq, part_val, part_idx);
+    } else {
+        unsigned grid = (unsigned)gpx_acq_parts(M);
+        acq_reduce_narrow_kernel<<<grid, A_THREADS, 0, (cudaStream_t)stream>>>(
+            S, M, mu, var, acq, coef, y_max, mu_scale, mu_shift, sd_scale, m_offset, out_mu,
+            out_sd, out_acq, part_val, part_idx);
+    }
     count_launches(1);
     GPX_LAUNCH_CHECK();
     return 0;

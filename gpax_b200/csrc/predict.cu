@@ -34,6 +34,7 @@
 #include <cuda.h>
 #include <cstdlib>
 #include "predict_small.cuh"
+#include "predict_tiny.cuh"
 
 namespace gpx {
 
@@ -226,7 +227,7 @@ predict_ws_kernel(const __grid_constant__ CUtensorMap tmW, gpx_kernel_params kp,
                   int M, const double *__restrict__ xs, const double *__restrict__ xnew,
                   const double *__restrict__ m_new, double m_const,
                   const double *__restrict__ diag_add, double *__restrict__ mu,
-                  double *__restrict__ var) {
+                  double *__restrict__ var, int64_t ldo, int64_t ldmn) {
     using C = WCfg<WN>;
     constexpr int WM = C::WM, GEN = C::GEN, D = W_GEN_AHEAD, XSP = DMAX + 2;
     constexpr bool Z_IN_REGS = (DMAX <= 4);
@@ -537,13 +538,13 @@ predict_ws_kernel(const __grid_constant__ CUtensorMap tmW, gpx_kernel_params kp,
             const double kd = (KIND == GPX_PERIODIC)
                                   ? scale
                                   : k_from_r2 < KIND == GPX_PERIODIC ? GPX_RBF : KIND > (0.0, scale);
-            if (var) var[(size_t)s * M + gj] = (kd + diag_add[s]) - colsum[t];
+            if (var) var[(size_t)s * ldo + gj] = (kd + diag_add[s]) - colsum[t];
             if (mu) {
-                const double m0 = m_new ? m_new[(size_t)s * M + gj] : m_const;
+                const double m0 = m_new ? m_new[(size_t)s * ldmn + gj] : m_const;
                 // entries of candidate t were generated by the threads with jb + 16 i == t
                 double dot = 0.0;
                 for (int k = 0; k < 16; ++k) dot += smean[(t >> 4) * W_THREADS + (t & 15) * 16 + k];
-                mu[(size_t)s * M + gj] = m0 + dot;
+                mu[(size_t)s * ldo + gj] = m0 + dot;
             }
         }
     }
@@ -590,7 +591,7 @@ template <int KIND, int WN, int DMAX>
 static int launch_predict_ws(const gpx_kernel_params *kp, int64_t S, int64_t n, int64_t M,
                              const double *xs, const double *xnew, const double *W, int64_t ldw,
                              const double *m_new, double m_const, const double *diag_add,
-                             double *mu, double *var, cudaStream_t st) {
+                             double *mu, double *var, int64_t ldo, int64_t ldmn, cudaStream_t st) {
     using C = WCfg<WN>;
     static bool configured = false;
     if (!configured) {
@@ -614,14 +615,14 @@ static int launch_predict_ws(const gpx_kernel_params *kp, int64_t S, int64_t n, 
             static bool cfg = false;                                                               \
             if (!cfg) { cudaFuncSetAttribute(predict_ws_kernel<GPX_MATERN52, 1, 2, D>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::SMEM_BYTES); cfg = true; } \
             predict_ws_kernel<GPX_MATERN52, 1, 2, D><<<grid, W_THREADS, C::SMEM_BYTES, st>>>(      \
-                tm, *kp, (int)n, n_pad, (int)M, xs, xnew, m_new, m_const, diag_add, mu, var);      \
+                tm, *kp, (int)n, n_pad, (int)M, xs, xnew, m_new, m_const, diag_add, mu, var, ldo, ldmn);      \
             return 0; }
         switch (dbg) { GPX_DBG_CASE(1) GPX_DBG_CASE(2) GPX_DBG_CASE(3) default: break; }
 #undef GPX_DBG_CASE
     }
 #endif
     predict_ws_kernel<KIND, WN, DMAX><<<grid, W_THREADS, C::SMEM_BYTES, st>>>(
-        tm, *kp, (int)n, n_pad, (int)M, xs, xnew, m_new, m_const, diag_add, mu, var);
+        tm, *kp, (int)n, n_pad, (int)M, xs, xnew, m_new, m_const, diag_add, mu, var, ldo, ldmn);
     return 0;
 }
 
@@ -629,11 +630,11 @@ template <int KIND, int WN>
 static int launch_predict_ws_d(const gpx_kernel_params *kp, int64_t S, int64_t n, int64_t M,
                                const double *xs, const double *xnew, const double *W, int64_t ldw,
                                const double *m_new, double m_const, const double *diag_add,
-                               double *mu, double *var, cudaStream_t st) {
+                               double *mu, double *var, int64_t ldo, int64_t ldmn, cudaStream_t st) {
     switch (dmax_of(kp->d)) {
-        case 2: return launch_predict_ws<KIND, WN, 2>(kp, S, n, M, xs, xnew, W, ldw, m_new, m_const, diag_add, mu, var, st);
-        case 4: return launch_predict_ws<KIND, WN, 4>(kp, S, n, M, xs, xnew, W, ldw, m_new, m_const, diag_add, mu, var, st);
-        default: return launch_predict_ws<KIND, WN, 8>(kp, S, n, M, xs, xnew, W, ldw, m_new, m_const, diag_add, mu, var, st);
+        case 2: return launch_predict_ws<KIND, WN, 2>(kp, S, n, M, xs, xnew, W, ldw, m_new, m_const, diag_add, mu, var, ldo, ldmn, st);
+        case 4: return launch_predict_ws<KIND, WN, 4>(kp, S, n, M, xs, xnew, W, ldw, m_new, m_const, diag_add, mu, var, ldo, ldmn, st);
+        default: return launch_predict_ws<KIND, WN, 8>(kp, S, n, M, xs, xnew, W, ldw, m_new, m_const, diag_add, mu, var, ldo, ldmn, st);
     }
 }
 
@@ -641,22 +642,24 @@ template <int KIND>
 static int dispatch_predict(const gpx_kernel_params *kp, int64_t S, int64_t n, int64_t M,
                             const double *x, const double *xnew, const double *W, int64_t ldw,
                             const double *alpha, const double *m_new, double m_const,
-                            const double *diag_add, double *mu, double *var, double *ws,
-                            cudaStream_t st) {
+                            const double *diag_add, double *mu, double *var, int64_t ldo,
+                            int64_t ldmn, bool prep, double *ws, cudaStream_t st) {
     // small n: the whole W fits one slab and the work is K*-generation bound
-    if (n <= 64)
-        return launch_predict<KIND, 1, 8, 16>(kp, S, n, M, x, xnew, W, ldw, alpha, m_new, m_const, diag_add, mu, var, st);
+    if (n <= 64)   // persistent warp-independent kernel (predict_tiny.cuh)
+        return launch_predict_tiny<KIND>(kp, S, n, M, x, xnew, W, ldw, alpha, m_new, m_const, diag_add, mu, var, ldo, ldmn, st);
     if (n <= 128)
-        return launch_predict<KIND, 2, 4, 16>(kp, S, n, M, x, xnew, W, ldw, alpha, m_new, m_const, diag_add, mu, var, st);
+        return launch_predict<KIND, 2, 4, 16>(kp, S, n, M, x, xnew, W, ldw, alpha, m_new, m_const, diag_add, mu, var, ldo, ldmn, st);
     if (!ws) { set_error("gpx_predict: workspace required for n > 128"); return -16; }
     const int n_pad = (int)((n + W_BK - 1) / W_BK * W_BK);
     dim3 g((unsigned)((n_pad + 255) / 256), (unsigned)S);
-    predict_prep_kernel<KIND><<<g, 256, 0, st>>>(*kp, (int)n, n_pad, x, alpha, ws);
-    count_launches(1);
+    if (prep) {   // per-sample scaled training inputs: once per (x, theta), not per candidate tile
+        predict_prep_kernel<KIND><<<g, 256, 0, st>>>(*kp, (int)n, n_pad, x, alpha, ws);
+        count_launches(1);
+    }
     // tall slabs amortise the K* regeneration for large n
     if (n <= 512)
-        return launch_predict_ws_d<KIND, 2>(kp, S, n, M, ws, xnew, W, ldw, m_new, m_const, diag_add, mu, var, st);
-    return launch_predict_ws_d<KIND, 1>(kp, S, n, M, ws, xnew, W, ldw, m_new, m_const, diag_add, mu, var, st);
+        return launch_predict_ws_d<KIND, 2>(kp, S, n, M, ws, xnew, W, ldw, m_new, m_const, diag_add, mu, var, ldo, ldmn, st);
+    return launch_predict_ws_d<KIND, 1>(kp, S, n, M, ws, xnew, W, ldw, m_new, m_const, diag_add, mu, var, ldo, ldmn, st);
 }
 
 }  // namespace gpx
@@ -667,11 +670,34 @@ extern "C" size_t gpx_predict_ws_bytes(int64_t S, int64_t n, int32_t d) {
     return (size_t)S * n_pad * (size_t)(gpx::dmax_of(d) + 2) * sizeof(double);
 }
 
-extern "C" int gpx_predict(const gpx_kernel_params *kp, int64_t S, int64_t n, int64_t M,
-                           const double *x, const double *xnew, const double *W, int64_t ldw,
-                           const double *alpha, const double *m_new, double m_const,
-                           const double *diag_add, double *mu, double *var, void *ws,
-                           void *stream) {
+// strided core shared by gpx_predict (ldo = ldmn = M) and the candidate-tiled gpx_predict_acq
+static int predict_core(const gpx_kernel_params *kp, int64_t S, int64_t n, int64_t M,
+                        const double *x, const double *xnew, const double *W, int64_t ldw,
+                        const double *alpha, const double *m_new, double m_const,
+                        const double *diag_add, double *mu, double *var, int64_t ldo, int64_t ldmn,
+                        bool prep, void *ws, cudaStream_t st) {
+    using namespace gpx;
+    int rc;
+    switch (kp->kind) {
+        case GPX_RBF:
+            rc = dispatch_predict<GPX_RBF>(kp, S, n, M, x, xnew, W, ldw, alpha, m_new, m_const, diag_add, mu, var, ldo, ldmn, prep, (double *)ws, st);
+            break;
+        case GPX_MATERN52:
+            rc = dispatch_predict<GPX_MATERN52>(kp, S, n, M, x, xnew, W, ldw, alpha, m_new, m_const, diag_add, mu, var, ldo, ldmn, prep, (double *)ws, st);
+            break;
+        default:
+            rc = dispatch_predict<GPX_PERIODIC>(kp, S, n, M, x, xnew, W, ldw, alpha, m_new, m_const, diag_add, mu, var, ldo, ldmn, prep, (double *)ws, st);
+            break;
+    }
+    if (rc) return rc;
+    count_launches(1);
+    GPX_LAUNCH_CHECK();
+    return 0;
+}
+
+static int predict_check_args(const gpx_kernel_params *kp, int64_t S, int64_t n, int64_t M,
+                              const double *x, const double *xnew, const double *W, int64_t ldw,
+                              const double *alpha, const double *diag_add) {
     using namespace gpx;
     GPX_ARG_CHECK(validate_kp(kp) == 0, 1);
     GPX_ARG_CHECK(S >= 0 && S <= 65535, 2);
@@ -684,23 +710,85 @@ extern "C" int gpx_predict(const gpx_kernel_params *kp, int64_t S, int64_t n, in
     GPX_ARG_CHECK(((uintptr_t)W & 15) == 0, 7);
     GPX_ARG_CHECK(alpha != nullptr || S * n == 0, 9);
     GPX_ARG_CHECK(diag_add != nullptr || S == 0, 12);
+    return 0;
+}
+
+extern "C" int gpx_predict(const gpx_kernel_params *kp, int64_t S, int64_t n, int64_t M,
+                           const double *x, const double *xnew, const double *W, int64_t ldw,
+                           const double *alpha, const double *m_new, double m_const,
+                           const double *diag_add, double *mu, double *var, void *ws,
+                           void *stream) {
+    using namespace gpx;
+    if (int rc = predict_check_args(kp, S, n, M, x, xnew, W, ldw, alpha, diag_add)) return rc;
     GPX_ARG_CHECK(ws != nullptr || gpx_predict_ws_bytes(S, n, kp->d) == 0, 15);
     if (S == 0 || M == 0) return 0;
+    return predict_core(kp, S, n, M, x, xnew, W, ldw, alpha, m_new, m_const, diag_add, mu, var, M, M,
+                        true, ws, (cudaStream_t)stream);
+}
+
+// ---------------------------------------------------------------------------
+// gpx_predict_acq: fused predictive + acquisition sweep over a candidate grid.
+// Candidates are walked in tiles of m_tile; each tile's per-sample moments
+// [S, m_tile] live only in the caller's workspace (sized to stay L2-resident, so
+// neither K* nor the moments make an HBM round trip) and are reduced over the
+// samples in the fixed order s = 0..S-1 right after they are produced.
+// ---------------------------------------------------------------------------
+extern "C" int64_t gpx_predict_acq_tile(int64_t S, int64_t M) {
+    // 16*S*m_tile bytes of moments <= 48 MiB (well inside the 126 MB L2), multiple of the
+    // acquisition block (256 candidates) so tile winners land on gpx_acq_parts(M) slots
+    if (S < 1) S = 1;
+    int64_t t = ((int64_t)48 << 20) / (16 * S);
+    t = t / 256 * 256;
+    if (t < 256) t = 256;
+    const int64_t m_up = (M + 255) / 256 * 256;
+    if (M > 0 && t > m_up) t = m_up;
+    return t;
+}
+
+extern "C" size_t gpx_predict_acq_ws_bytes(int64_t S, int64_t n, int32_t d, int64_t m_tile) {
+    if (S <= 0 || m_tile <= 0) return 0;
+    size_t pw = (gpx_predict_ws_bytes(S, n, d) + 255) / 256 * 256;
+    return pw + 2 * (size_t)S * (size_t)m_tile * sizeof(double);
+}
+
+extern "C" int gpx_predict_acq(const gpx_kernel_params *kp, int64_t S, int64_t n, int64_t M,
+                               const double *x, const double *xnew, const double *W, int64_t ldw,
+                               const double *alpha, const double *m_new, double m_const,
+                               const double *diag_add, int32_t acq, double beta, double y_max,
+                               double mu_scale, double mu_shift, double sd_scale,
+                               int64_t m_offset, int64_t m_tile, double *out_mu, double *out_sd,
+                               double *out_acq, double *part_val, int64_t *part_idx,
+                               double *best_val, int64_t *best_idx, void *ws, void *stream) {
+    using namespace gpx;
+    if (int rc = predict_check_args(kp, S, n, M, x, xnew, W, ldw, alpha, diag_add)) return rc;
+    GPX_ARG_CHECK(S >= 1, 2);
+    GPX_ARG_CHECK(acq >= GPX_ACQ_EI && acq <= GPX_ACQ_MEAN, 13);
+    GPX_ARG_CHECK(!(acq == GPX_ACQ_UCB) || beta >= 0.0, 14);
+    GPX_ARG_CHECK(m_tile >= 256 && m_tile % 256 == 0, 20);
+    GPX_ARG_CHECK(part_val != nullptr && part_idx != nullptr, 24);
+    GPX_ARG_CHECK(ws != nullptr, 28);
+    if (M == 0) return 0;
     cudaStream_t st = (cudaStream_t)stream;
-    int rc;
-    switch (kp->kind) {
-        case GPX_RBF:
-            rc = dispatch_predict<GPX_RBF>(kp, S, n, M, x, xnew, W, ldw, alpha, m_new, m_const, diag_add, mu, var, (double *)ws, st);
-            break;
-        case GPX_MATERN52:
-            rc = dispatch_predict<GPX_MATERN52>(kp, S, n, M, x, xnew, W, ldw, alpha, m_new, m_const, diag_add, mu, var, (double *)ws, st);
-            break;
-        default:
-            rc = dispatch_predict<GPX_PERIODIC>(kp, S, n, M, x, xnew, W, ldw, alpha, m_new, m_const, diag_add, mu, var, (double *)ws, st);
-            break;
+    const size_t pw = (gpx_predict_ws_bytes(S, n, kp->d) + 255) / 256 * 256;
+    double *t_mu = (double *)((char *)ws + pw);
+    double *t_var = t_mu + (size_t)S * m_tile;
+    const int d = kp->d;
+    bool prep = true;
+    for (int64_t j0 = 0; j0 < M; j0 += m_tile) {
+        const int64_t mt = (M - j0 < m_tile) ? (M - j0) : m_tile;
+        int rc = predict_core(kp, S, n, mt, x, xnew + j0 * d, W, ldw, alpha,
+                              m_new ? m_new + j0 : nullptr, m_const, diag_add, t_mu, t_var, mt, M,
+                              prep, ws, st);
+        if (rc) return rc;
+        prep = false;
+        const int64_t p0 = j0 / 32;   // gpx_acq_parts granularity
+        rc = gpx_acq_reduce(S, mt, t_mu, t_var, acq, beta, y_max, mu_scale, mu_shift, sd_scale,
+                            m_offset + j0, out_mu ? out_mu + j0 : nullptr,
+                            out_sd ? out_sd + j0 : nullptr, out_acq ? out_acq + j0 : nullptr,
+                            part_val + p0, part_idx + p0, stream);
+        if (rc) return rc;
     }
-    if (rc) return rc;
-    count_launches(1);
-    GPX_LAUNCH_CHECK();
+    if (best_val || best_idx)
+        return gpx_argmax_finalize(gpx_acq_parts(M), part_val, part_idx, best_val, best_idx, stream);
     return 0;
 }

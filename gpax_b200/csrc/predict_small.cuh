@@ -59,7 +59,7 @@ predict_kernel(gpx_kernel_params kp, int n, int M, const double *__restrict__ x,
                const double *__restrict__ xnew, const double *__restrict__ W, int64_t ldw,
                const double *__restrict__ alpha, const double *__restrict__ m_new, double m_const,
                const double *__restrict__ diag_add, double *__restrict__ mu,
-               double *__restrict__ var) {
+               double *__restrict__ var, int64_t ldo, int64_t ldmn) {
     using C = PCfg<WM, WN, BK>;
     extern __shared__ __align__(16) double sm[];
     double *sW = sm;
@@ -279,12 +279,12 @@ predict_kernel(gpx_kernel_params kp, int n, int M, const double *__restrict__ x,
         const int gj = j0 + t;
         if (gj < M) {
             double kd = (KIND == GPX_PERIODIC) ? scale : k_from_r2<KIND == GPX_PERIODIC ? GPX_RBF : KIND>(0.0, scale);
-            if (var) var[(size_t)s * M + gj] = (kd + diag_add[s]) - colsum[t];
+            if (var) var[(size_t)s * ldo + gj] = (kd + diag_add[s]) - colsum[t];
             if (mu) {
-                double m0 = m_new ? m_new[(size_t)s * M + gj] : m_const;
+                double m0 = m_new ? m_new[(size_t)s * ldmn + gj] : m_const;
                 double dot = 0.0;
                 for (int q = t; q < P_THREADS; q += C::MT) dot += smean[q];
-                mu[(size_t)s * M + gj] = m0 + dot;
+                mu[(size_t)s * ldo + gj] = m0 + dot;
             }
         }
     }
@@ -294,7 +294,7 @@ template <int KIND, int WM, int WN, int BK>
 static int launch_predict(const gpx_kernel_params *kp, int64_t S, int64_t n, int64_t M,
                           const double *x, const double *xnew, const double *W, int64_t ldw,
                           const double *alpha, const double *m_new, double m_const,
-                          const double *diag_add, double *mu, double *var, cudaStream_t st) {
+                          const double *diag_add, double *mu, double *var, int64_t ldo, int64_t ldmn, cudaStream_t st) {
     using C = PCfg<WM, WN, BK>;
     const size_t smem = C::SMEM_DOUBLES * sizeof(double);
     static bool configured = false;
@@ -306,7 +306,7 @@ static int launch_predict(const gpx_kernel_params *kp, int64_t S, int64_t n, int
     }
     dim3 grid((unsigned)((M + C::MT - 1) / C::MT), (unsigned)S);
     predict_kernel<KIND, WM, WN, BK><<<grid, P_THREADS, smem, st>>>(
-        *kp, (int)n, (int)M, x, xnew, W, ldw, alpha, m_new, m_const, diag_add, mu, var);
+        *kp, (int)n, (int)M, x, xnew, W, ldw, alpha, m_new, m_const, diag_add, mu, var, ldo, ldmn);
     return 0;
 }
 

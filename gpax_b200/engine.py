@@ -203,6 +203,37 @@ def acq_reduce(mu, var, acq, beta=10.0, y_max=0.0, mu_scale=1.0, mu_shift=0.0, s
     return o_mu, o_sd, o_acq, pv, pi
 
 
+def predict_acq(hpd: HyperParams, x, x_new, W, alpha, diag_add, acq, beta=10.0, y_max=0.0,
+                mu_scale=1.0, mu_shift=0.0, sd_scale=1.0, m_offset=0, m_new=None, m_const=1.0,
+                m_tile=None, want_arrays=True, ws=None):
+    """Fused predictive + acquisition sweep (``gpx_predict_acq``): per-sample moments only
+    ever exist for one L2-resident candidate tile.  Returns
+    ``(out_mu, out_sd, out_acq, best_val[1], best_idx[1])`` (arrays None unless wanted)."""
+    S, n, M = hpd.S, x.shape[0], x_new.shape[0]
+    dev = x.device
+    if m_new is not None and tuple(m_new.shape) != (S, M):
+        raise ValueError(f"m_new must have shape (S, M) = ({S}, {M}), got {tuple(m_new.shape)}")
+    mt = int(m_tile) if m_tile else lib.gpx_predict_acq_tile(S, M)
+    nbytes = lib.gpx_predict_acq_ws_bytes(S, n, hpd.d, mt)
+    if ws is None or ws.numel() * 8 < nbytes:
+        ws = torch.empty(max(1, nbytes // 8), dtype=F64, device=dev)
+    P = max(1, lib.gpx_acq_parts(M))
+    o_mu = torch.empty(M, dtype=F64, device=dev) if want_arrays else None
+    o_sd = torch.empty(M, dtype=F64, device=dev) if want_arrays else None
+    o_acq = torch.empty(M, dtype=F64, device=dev) if want_arrays else None
+    pv = torch.empty(P, dtype=F64, device=dev)
+    pi = torch.empty(P, dtype=torch.int64, device=dev)
+    bv = torch.empty(1, dtype=F64, device=dev)
+    bi = torch.empty(1, dtype=torch.int64, device=dev)
+    check(lib.gpx_predict_acq(C.byref(hpd.kp), S, n, M, _ptr(x), _ptr(x_new), _ptr(W), W.shape[2],
+                              _ptr(alpha), _ptr(m_new), float(m_const), _ptr(diag_add), int(acq),
+                              float(beta), float(y_max), float(mu_scale), float(mu_shift),
+                              float(sd_scale), int(m_offset), mt, _ptr(o_mu), _ptr(o_sd),
+                              _ptr(o_acq), _ptr(pv), _ptr(pi), _ptr(bv), _ptr(bi), _ptr(ws),
+                              _stream()), "gpx_predict_acq")
+    return o_mu, o_sd, o_acq, bv, bi
+
+
 def argmax_finalize(pv, pi):
     dev = pv.device
     bv = torch.empty(1, dtype=F64, device=dev)
@@ -254,6 +285,17 @@ class Posterior:
         mn = _dev(m_new, self.dev) if m_new is not None else None
         return predict(self.hpd, self.x, xn, self.W, self.alpha, diag_add.contiguous(), mn,
                        m_const, want_mu, want_var)
+
+    def predict_acq(self, x_new, acq, beta=10.0, y_max=0.0, mu_scale=1.0, mu_shift=0.0,
+                    sd_scale=1.0, m_offset=0, m_new=None, m_const=1.0, observation_noise=False,
+                    m_tile=None, want_arrays=True):
+        xn = _dev(np.asarray(x_new, float).reshape(len(x_new), -1), self.dev) \
+            if not isinstance(x_new, torch.Tensor) else x_new
+        diag_add = (self.hpd.noise + self.hpd.jitter) if observation_noise else self.hpd.jitter
+        mn = _dev(m_new, self.dev) if m_new is not None else None
+        return predict_acq(self.hpd, self.x, xn, self.W, self.alpha, diag_add.contiguous(), acq,
+                           beta, y_max, mu_scale, mu_shift, sd_scale, m_offset, mn, m_const,
+                           m_tile, want_arrays)
 
     def grad(self):
         g = mll_grad(self.hpd, self.x, self.W, self.alpha)

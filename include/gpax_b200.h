@@ -37,7 +37,7 @@
 extern "C" {
 #endif
 
-#define GPX_ABI_VERSION 3
+#define GPX_ABI_VERSION 4
 
 /* covariance families: gpax/kernels.py:110 (RBF), :129 (Matern nu=5/2), :150 (Periodic) */
 enum { GPX_RBF = 0, GPX_MATERN52 = 1, GPX_PERIODIC = 2 };
@@ -178,6 +178,36 @@ int gpx_acq_reduce(int64_t S, int64_t M, const double *mu, const double *var,
                    double *part_val, int64_t *part_idx, void *stream);
 int gpx_argmax_finalize(int64_t P, const double *part_val, const int64_t *part_idx,
                         double *best_val, int64_t *best_idx, void *stream);
+
+/* ---------------------------------------------------------------------------
+ * gpx_predict_acq: the fused posterior predictive + acquisition sweep over a
+ * candidate grid (north_star item 3) -- what AcquisitionFunction.__call__
+ * (gpax/acquisition.py:133-164) evaluates through model.sample/predict
+ * (gpax/gp.py:399-501) and what _optimize_halton (gpax/acquisition.py:203-214)
+ * loops over in chunks of 100, here in one call.  Candidates are walked in tiles
+ * of m_tile (multiple of 256; gpx_predict_acq_tile(S, M) picks one whose [S, m_tile]
+ * moments, 16*S*m_tile bytes, stay L2-resident); per tile gpx_predict writes the
+ * per-sample moments into `ws` and gpx_acq_reduce consumes them at once, so neither
+ * K* nor mu/var[S, M] ever make an HBM round trip and no [S, M] buffer exists.
+ * Arguments are those of gpx_predict followed by those of gpx_acq_reduce;
+ * part_val/part_idx [gpx_acq_parts(M)]; best_val/best_idx (nullable) receive the
+ * first maximum over this call's M candidates (global index m_offset + j), ready
+ * for the all-gather + gpx_argmax_finalize across GPUs when M is sharded.
+ *   ws: gpx_predict_acq_ws_bytes(S, n, d, m_tile) bytes.
+ * Bit-identical to gpx_predict -> gpx_acq_reduce on the whole grid for any m_tile.
+ */
+int64_t gpx_predict_acq_tile(int64_t S, int64_t M);
+size_t gpx_predict_acq_ws_bytes(int64_t S, int64_t n, int32_t d, int64_t m_tile);
+int gpx_predict_acq(const gpx_kernel_params *kp, int64_t S, int64_t n, int64_t M,
+                    const double *x, const double *xnew,
+                    const double *W, int64_t ldw, const double *alpha,
+                    const double *m_new, double m_const, const double *diag_add,
+                    int32_t acq, double beta, double y_max,
+                    double mu_scale, double mu_shift, double sd_scale,
+                    int64_t m_offset, int64_t m_tile,
+                    double *out_mu, double *out_sd, double *out_acq,
+                    double *part_val, int64_t *part_idx,
+                    double *best_val, int64_t *best_idx, void *ws, void *stream);
 
 #ifdef __cplusplus
 }

@@ -158,7 +158,9 @@ def test_mll_grad_matches_oracle(cuda, kind, per):
 
 
 @pytest.mark.parametrize("acq,beta", [(0, 0.0), (1, 10.0), (1, float("inf")), (1, 0.0), (2, 0.0), (3, 0.0)])
-@pytest.mark.parametrize("S,M", [(1, 1000), (17, 5003)])
+# M < 303104 runs the narrow (32 candidates / CTA) kernel, larger M the wide one; S = 70 and 33
+# cross the narrow kernel's 32-sample chunk boundary with a ragged tail
+@pytest.mark.parametrize("S,M", [(1, 1000), (17, 5003), (70, 999), (33, 64), (1, 303200), (5, 310001)])
 def test_acq_reduce_bit_exact(cuda, acq, beta, S, M):
     """Mixture moments + EI/UCB/UE + argmax.  Moments and UCB are bit-exact vs the
     NumPy oracle (same operation order, no FMA); EI within 1e-13 relative (erf/exp
@@ -440,3 +442,51 @@ def test_c3_full_size_acquisition_sweep(cuda):
         torch.cuda.synchronize()
         assert int(bi.item()) == int(np.argmax(full_acq))
         assert float(bv.item()) == float(full_acq[int(bi.item())])
+
+
+@pytest.mark.parametrize("kind,per,n,d,S,M,m_tile,with_mean", [
+    ("rbf", False, 64, 1, 9, 1000, 256, False),
+    ("matern52", False, 100, 2, 5, 777, 512, True),
+    ("periodic", True, 129, 1, 3, 600, 256, False),
+    ("matern52", False, 300, 2, 4, 1500, None, True),
+    ("rbf", False, 640, 2, 3, 530, 256, False),
+])
+def test_predict_acq_fused_equals_two_stage(cuda, kind, per, n, d, S, M, m_tile, with_mean):
+    """gpx_predict_acq (candidate-tiled fused sweep) must be bit-identical to
+    gpx_predict -> gpx_acq_reduce -> gpx_argmax_finalize on the whole grid, for any tile
+    width, with the global index offset applied; and match the oracle's mixture + EI/UCB."""
+    import torch
+    from gpax_b200 import engine as E, _cabi
+    x, y, xn, hp = _mk(kind, n, d, S, M, 900 + n, ard=(d == 2), period=per)
+    rng = np.random.default_rng(1)
+    mt = rng.normal(size=(S, n)) if with_mean else None
+    mn = rng.normal(size=(S, M)) if with_mean else None
+    post = E.Posterior(kind, x, y, hp, m_train=mt, device=cuda)
+    y_max, a, b, c, off = float(y.max()), 1.3, 0.2, 1.3, 12345
+    mu, var = post.predict(xn, m_new=mn)
+    for acq, beta in ((_cabi.ACQ_EI, 0.0), (_cabi.ACQ_UCB, 10.0), (_cabi.ACQ_UE, 0.0)):
+        r_mu, r_sd, r_acq, pv, pi = E.acq_reduce(mu, var, acq, beta, y_max, a, b, c, m_offset=off)
+        r_bv, r_bi = E.argmax_finalize(pv, pi)
+        f_mu, f_sd, f_acq, f_bv, f_bi = post.predict_acq(xn, acq, beta, y_max, a, b, c, m_offset=off,
+                                                         m_new=mn, m_tile=m_tile)
+        torch.cuda.synchronize()
+        assert torch.equal(f_mu, r_mu) and torch.equal(f_sd, r_sd)
+        assert torch.equal(f_acq, r_acq)
+        assert int(f_bi.item()) == int(r_bi.item()) and float(f_bv.item()) == float(r_bv.item())
+        assert off <= int(f_bi.item()) < off + M
+    mu_o, var_o = O.predict_batched(kind, x, y, xn, hp, m_train=mt, m_new=mn, diag_only=True)
+    mbar, vbar = O.mixture_moments(mu_o, var_o)
+    ref = O.acquisition(_cabi.ACQ_UE, mbar * a + b, np.sqrt(vbar) * c, 0.0, y_max)
+    assert _rel(f_acq.cpu().numpy(), ref) < 1e-9
+
+
+def test_predict_acq_argument_errors(cuda):
+    import torch
+    from gpax_b200 import engine as E, _cabi
+    x, y, xn, hp = _mk("rbf", 40, 1, 3, 300, 7)
+    post = E.Posterior("rbf", x, y, hp, device=cuda)
+    with pytest.raises(_cabi.GpxError):
+        post.predict_acq(xn, _cabi.ACQ_EI, m_tile=100)        # not a multiple of 256
+    with pytest.raises(_cabi.GpxError):
+        post.predict_acq(xn, _cabi.ACQ_UCB, beta=-1.0)
+    torch.cuda.synchronize()
