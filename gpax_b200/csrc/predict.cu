@@ -65,6 +65,15 @@ struct WCfg {
 
 // workspace row: DMAX scaled coordinates (zero padded), squared norm, alpha
 __host__ __device__ constexpr int dmax_of(int d) { return d <= 2 ? 2 : (d <= 4 ? 4 : 8); }
+// Internal kind of the n > 128 path: Periodic with d <= 4 evaluated through angle-addition
+// features instead of one sin per (train point, candidate, dimension):
+//   sin(pi (z - x) / p) / l = cB * (sA / l) - sB * (cA / l),  A = pi x / p,  B = pi z / p,
+// so a train point is staged as f = [sA/l, cA/l]_q and a candidate as g = [cB, -sB]_q (2d
+// "coordinates") and the periodic sum of gpax/kernels.py:163-165 is sum_q (f_2q g_2q + f_2q+1 g_2q+1)^2:
+// 3 FP64 instructions per dimension on the pipe the DMMAs need, instead of ~100.  The absolute
+// error of each sine stays at the 1e-16 level of the reference's own sin(pi * diff / period).
+constexpr int GPX_PERIODIC_FEAT = 3;
+__host__ __device__ constexpr int feat_dim(int kind, int d) { return kind == GPX_PERIODIC_FEAT ? 2 * d : d; }
 
 // ---- mbarrier / TMA / shared-memory primitives (PTX) -------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void *p) {
@@ -125,11 +134,22 @@ predict_prep_kernel(gpx_kernel_params kp, int n, int n_pad, const double *__rest
     const int64_t s = blockIdx.y;
     const int k = blockIdx.x * 256 + threadIdx.x;
     if (k >= n_pad) return;
-    const int d = kp.d, DM = dmax_of(d), XSP = DM + 2;
+    const int d = kp.d, DM = dmax_of(feat_dim(KIND, d)), XSP = DM + 2;
     double *dst = xs + ((size_t)s * n_pad + k) * XSP;
     for (int q = 0; q < XSP; ++q) dst[q] = 0.0;
     if (k >= n) return;      // padding rows: finite values, alpha = 0 (W columns >= n read as 0)
     double nrm = 0.0;
+    if (KIND == GPX_PERIODIC_FEAT) {
+        for (int q = 0; q < d; ++q) {
+            double sn, cs;
+            sincos(GPX_PI * x[(size_t)k * d + q] / per_of(kp, s, q), &sn, &cs);
+            const double l = len_of(kp, s, q);
+            dst[2 * q] = sn / l;
+            dst[2 * q + 1] = cs / l;
+        }
+        dst[DM + 1] = alpha[(size_t)s * n + k];
+        return;
+    }
     for (int q = 0; q < d; ++q) {
         double v = x[(size_t)k * d + q];
         if (KIND != GPX_PERIODIC) v = v / len_of(kp, s, q);
@@ -274,11 +294,20 @@ predict_ws_kernel(const __grid_constant__ CUtensorMap tmW, gpx_kernel_params kp,
     for (int e = t; e < C::MT; e += W_THREADS) {
         const int gj = j0 + e;
         double nrm = 0.0;
-        for (int q = 0; q < GPX_MAX_D; ++q) {
-            double v = (gj < M && q < d) ? xnew[(size_t)gj * d + q] : 0.0;
-            if (KIND != GPX_PERIODIC) v = v / s_len[q];
-            sZ[e * (GPX_MAX_D + 1) + q] = v;
-            nrm += v * v;
+        if (KIND == GPX_PERIODIC_FEAT) {
+            for (int q = 0; q < GPX_MAX_D / 2; ++q) {
+                double sn = 0.0, cs = 0.0;
+                if (gj < M && q < d) sincos(GPX_PI * xnew[(size_t)gj * d + q] / s_per[q], &sn, &cs);
+                sZ[e * (GPX_MAX_D + 1) + 2 * q] = cs;
+                sZ[e * (GPX_MAX_D + 1) + 2 * q + 1] = -sn;
+            }
+        } else {
+            for (int q = 0; q < GPX_MAX_D; ++q) {
+                double v = (gj < M && q < d) ? xnew[(size_t)gj * d + q] : 0.0;
+                if (KIND != GPX_PERIODIC) v = v / s_len[q];
+                sZ[e * (GPX_MAX_D + 1) + q] = v;
+                nrm += v * v;
+            }
         }
         sZ[e * (GPX_MAX_D + 1) + GPX_MAX_D] = nrm;
     }
@@ -341,7 +370,15 @@ predict_ws_kernel(const __grid_constant__ CUtensorMap tmW, gpx_kernel_params kp,
             for (int q = 0; q <= DMAX; ++q)
                 zq[q] = Z_IN_REGS ? zr[Z_IN_REGS ? i : 0][Z_IN_REGS ? q : 0]
                                   : sZ[(jb + 16 * i) * (GPX_MAX_D + 1) + (q < DMAX ? q : GPX_MAX_D)];
-            if (KIND == GPX_PERIODIC) {
+            if (KIND == GPX_PERIODIC_FEAT) {
+                double acc = 0.0;
+#pragma unroll
+                for (int q = 0; q < DMAX; q += 2) {
+                    const double sn = fma(zq[q], xr_at(q), zq[q + 1] * xr_at(q + 1));
+                    acc = fma(sn, sn, acc);
+                }
+                g.v[i] = acc;
+            } else if (KIND == GPX_PERIODIC) {
                 double acc = 0.0;
 #pragma unroll
                 for (int q = 0; q < DMAX; ++q) {
@@ -535,9 +572,9 @@ predict_ws_kernel(const __grid_constant__ CUtensorMap tmW, gpx_kernel_params kp,
     if (t < C::MT) {
         const int gj = j0 + t;
         if (gj < M) {
-            const double kd = (KIND == GPX_PERIODIC)
+            const double kd = (KIND == GPX_PERIODIC || KIND == GPX_PERIODIC_FEAT)
                                   ? scale
-                                  : k_from_r2 < KIND == GPX_PERIODIC ? GPX_RBF : KIND > (0.0, scale);
+                                  : k_from_r2 < (KIND == GPX_PERIODIC || KIND == GPX_PERIODIC_FEAT) ? GPX_RBF : KIND > (0.0, scale);
             if (var) var[(size_t)s * ldo + gj] = (kd + diag_add[s]) - colsum[t];
             if (mu) {
                 const double m0 = m_new ? m_new[(size_t)s * ldmn + gj] : m_const;
@@ -631,11 +668,14 @@ static int launch_predict_ws_d(const gpx_kernel_params *kp, int64_t S, int64_t n
                                const double *xs, const double *xnew, const double *W, int64_t ldw,
                                const double *m_new, double m_const, const double *diag_add,
                                double *mu, double *var, int64_t ldo, int64_t ldmn, cudaStream_t st) {
-    switch (dmax_of(kp->d)) {
-        case 2: return launch_predict_ws<KIND, WN, 2>(kp, S, n, M, xs, xnew, W, ldw, m_new, m_const, diag_add, mu, var, ldo, ldmn, st);
-        case 4: return launch_predict_ws<KIND, WN, 4>(kp, S, n, M, xs, xnew, W, ldw, m_new, m_const, diag_add, mu, var, ldo, ldmn, st);
-        default: return launch_predict_ws<KIND, WN, 8>(kp, S, n, M, xs, xnew, W, ldw, m_new, m_const, diag_add, mu, var, ldo, ldmn, st);
-    }
+    if constexpr (KIND == GPX_PERIODIC)   // sin path: only d > 4 gets here (see dispatch_predict)
+        return launch_predict_ws<KIND, WN, 8>(kp, S, n, M, xs, xnew, W, ldw, m_new, m_const, diag_add, mu, var, ldo, ldmn, st);
+    else
+        switch (dmax_of(feat_dim(KIND, kp->d))) {
+            case 2: return launch_predict_ws<KIND, WN, 2>(kp, S, n, M, xs, xnew, W, ldw, m_new, m_const, diag_add, mu, var, ldo, ldmn, st);
+            case 4: return launch_predict_ws<KIND, WN, 4>(kp, S, n, M, xs, xnew, W, ldw, m_new, m_const, diag_add, mu, var, ldo, ldmn, st);
+            default: return launch_predict_ws<KIND, WN, 8>(kp, S, n, M, xs, xnew, W, ldw, m_new, m_const, diag_add, mu, var, ldo, ldmn, st);
+        }
 }
 
 template <int KIND>
@@ -652,11 +692,20 @@ static int dispatch_predict(const gpx_kernel_params *kp, int64_t S, int64_t n, i
     if (!ws) { set_error("gpx_predict: workspace required for n > 128"); return -16; }
     const int n_pad = (int)((n + W_BK - 1) / W_BK * W_BK);
     dim3 g((unsigned)((n_pad + 255) / 256), (unsigned)S);
+    // Periodic with d <= 4 runs on angle-addition features (GPX_PERIODIC_FEAT above)
+    constexpr int KF = (KIND == GPX_PERIODIC) ? GPX_PERIODIC_FEAT : KIND;
+    const bool feat = (KIND == GPX_PERIODIC) && kp->d <= GPX_MAX_D / 2;
     if (prep) {   // per-sample scaled training inputs: once per (x, theta), not per candidate tile
-        predict_prep_kernel<KIND><<<g, 256, 0, st>>>(*kp, (int)n, n_pad, x, alpha, ws);
+        if (feat) predict_prep_kernel<KF><<<g, 256, 0, st>>>(*kp, (int)n, n_pad, x, alpha, ws);
+        else predict_prep_kernel<KIND><<<g, 256, 0, st>>>(*kp, (int)n, n_pad, x, alpha, ws);
         count_launches(1);
     }
     // tall slabs amortise the K* regeneration for large n
+    if (feat) {
+        if (n <= 512)
+            return launch_predict_ws_d<KF, 2>(kp, S, n, M, ws, xnew, W, ldw, m_new, m_const, diag_add, mu, var, ldo, ldmn, st);
+        return launch_predict_ws_d<KF, 1>(kp, S, n, M, ws, xnew, W, ldw, m_new, m_const, diag_add, mu, var, ldo, ldmn, st);
+    }
     if (n <= 512)
         return launch_predict_ws_d<KIND, 2>(kp, S, n, M, ws, xnew, W, ldw, m_new, m_const, diag_add, mu, var, ldo, ldmn, st);
     return launch_predict_ws_d<KIND, 1>(kp, S, n, M, ws, xnew, W, ldw, m_new, m_const, diag_add, mu, var, ldo, ldmn, st);
@@ -667,7 +716,9 @@ static int dispatch_predict(const gpx_kernel_params *kp, int64_t S, int64_t n, i
 extern "C" size_t gpx_predict_ws_bytes(int64_t S, int64_t n, int32_t d) {
     if (n <= 128 || S <= 0) return 0;
     const size_t n_pad = (size_t)((n + gpx::W_BK - 1) / gpx::W_BK * gpx::W_BK);
-    return (size_t)S * n_pad * (size_t)(gpx::dmax_of(d) + 2) * sizeof(double);
+    // sized for the widest staging of any kind: Periodic with d <= 4 stages 2d features per point
+    const int dm = gpx::dmax_of(d <= GPX_MAX_D / 2 ? 2 * d : d);
+    return (size_t)S * n_pad * (size_t)(dm + 2) * sizeof(double);
 }
 
 // strided core shared by gpx_predict (ldo = ldmn = M) and the candidate-tiled gpx_predict_acq
@@ -734,10 +785,11 @@ extern "C" int gpx_predict(const gpx_kernel_params *kp, int64_t S, int64_t n, in
 // samples in the fixed order s = 0..S-1 right after they are produced.
 // ---------------------------------------------------------------------------
 extern "C" int64_t gpx_predict_acq_tile(int64_t S, int64_t M) {
-    // 16*S*m_tile bytes of moments <= 48 MiB (well inside the 126 MB L2), multiple of the
+    // 16*S*m_tile bytes of moments <= 256 MiB (measured: within 2 % of the unbounded two-stage
+    // sweep at C3; 48 MiB, i.e. L2-resident, costs 8 % in launch tails), multiple of the
     // acquisition block (256 candidates) so tile winners land on gpx_acq_parts(M) slots
     if (S < 1) S = 1;
-    int64_t t = ((int64_t)48 << 20) / (16 * S);
+    int64_t t = ((int64_t)256 << 20) / (16 * S);
     t = t / 256 * 256;
     if (t < 256) t = 256;
     const int64_t m_up = (M + 255) / 256 * 256;

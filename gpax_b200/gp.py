@@ -305,11 +305,25 @@ class GaussianProcess:
         x_new_t = self.input_transform.forward(np.asarray(x_new, float), transforms_as="mean")
         _, rng = state.get_rng_key()
         hp, _ = self._hp_for(rng, fast)
-        mu, var, _ = self._moments_device(x_new_t, hp)
         a, b, c = _affine_of(self.output_transform)
-        o_mu, o_sd, o_acq, pv, pi = E.acq_reduce(mu, var, acq, beta=beta, y_max=y_max, mu_scale=a,
-                                                 mu_shift=b, sd_scale=c, want_arrays=want_arrays)
-        bv, bi = E.argmax_finalize(pv, pi)
+        if self.x is not None:
+            # conditioned model: one fused gpx_predict_acq sweep, no [S, M] moment buffers
+            x_new_t = np.asarray(x_new_t, float).reshape(len(x_new_t), -1)
+            post = self._posterior(hp)
+            m_new = self._mean_values(x_new_t)
+            if np.all(m_new == m_new[0]):
+                kw = {"m_const": float(m_new[0])}
+            else:
+                kw = {"m_new": np.broadcast_to(m_new, (post.S, len(m_new))).copy()}
+            o_mu, o_sd, o_acq, bv, bi = post.predict_acq(
+                x_new_t, acq, beta=beta, y_max=y_max, mu_scale=a, mu_shift=b, sd_scale=c,
+                observation_noise=self.observation_noise, want_arrays=want_arrays, **kw)
+        else:
+            mu, var, _ = self._moments_device(x_new_t, hp)
+            o_mu, o_sd, o_acq, pv, pi = E.acq_reduce(mu, var, acq, beta=beta, y_max=y_max,
+                                                     mu_scale=a, mu_shift=b, sd_scale=c,
+                                                     want_arrays=want_arrays)
+            bv, bi = E.argmax_finalize(pv, pi)
         host = [None if t is None else t.cpu().numpy() for t in (o_mu, o_sd, o_acq)]
         return host[0], host[1], host[2], float(bv.item()), int(bi.item())
 

@@ -42,9 +42,9 @@ def test_cabi_size_queries_and_argument_errors():
     lib = _cabi.lib
     assert lib.gpx_dinv_bytes(3, 300) == 3 * 3 * 128 * 128 * 8
     assert lib.gpx_predict_ws_bytes(5, 100, 2) == 0
-    assert lib.gpx_predict_ws_bytes(5, 1000, 2) == 5 * 1008 * 4 * 8
-    assert lib.gpx_predict_ws_bytes(5, 1000, 3) == 5 * 1008 * 6 * 8
-    assert lib.gpx_acq_parts(1000) == 4
+    assert lib.gpx_predict_ws_bytes(5, 1000, 2) == 5 * 1008 * 6 * 8    # sized for 2d periodic features
+    assert lib.gpx_predict_ws_bytes(5, 1000, 3) == 5 * 1008 * 10 * 8
+    assert lib.gpx_acq_parts(1000) == 32      # one partial winner per 32 candidates
     assert lib.gpx_mll_grad_ws_bytes(2, 300, 2) > 0
     assert lib.gpx_mll_ws_bytes(3, 300) == 2 * 3 * 384 * 8
     kp = _cabi.KernelParams(7, 2, 1, 0, 0, 0, 0)        # invalid kind
