@@ -10,6 +10,7 @@
 // p only; each tile is read and written once -- used when S gives enough
 // parallelism) and RIGHT-looking (rank-NB update of the whole trailing matrix --
 // used for few large matrices, e.g. n = 16384, S = 1).
+#include <mutex>
 #include "mma_tile.cuh"
 
 namespace gpx {
@@ -137,12 +138,12 @@ diag_kernel(int64_t n, int p, double *__restrict__ A, int64_t lda, double *__res
 // tile kernels (one CTA = one 128x128 tile; blockIdx.y = sample)
 // ---------------------------------------------------------------------------
 enum { OP_SYRK_LEFT = 0, OP_SYRK_RIGHT = 1, OP_TRSM = 2, OP_TRTRI_ACC = 3, OP_TRTRI_FIN = 4,
-       OP_TRTRI_RIGHT = 5 };
+       OP_TRTRI_RIGHT = 5, OP_SYRK_COL = 6 };
 
 template <int OP>
 __global__ void __launch_bounds__(T_THREADS, 1)
 tile_kernel(int64_t n, int p, double *__restrict__ A, int64_t lda, const double *__restrict__ L,
-            int64_t ldl, const double *__restrict__ dinv) {
+            int64_t ldl, const double *__restrict__ dinv, int q0) {
     extern __shared__ __align__(16) double smem[];
     const int64_t s = blockIdx.y;
     const int T = (int)((n + NB - 1) / NB);
@@ -162,13 +163,21 @@ tile_kernel(int64_t n, int p, double *__restrict__ A, int64_t lda, const double 
         tile_gemm<false>(smem, a, b, (int64_t)p * NB, acc);
         tile_store<false>(As, lda, i * NB, (int64_t)p * NB, n, n, -1.0, true, acc);
     } else if (OP == OP_SYRK_RIGHT) {
-        // tile (i, j), p < j <= i < T from a triangular enumeration; K = block p
+        // tile (i, j), q0 <= j <= i < T from a triangular enumeration (q0 = p + 1: the whole
+        // trailing matrix; q0 = p + 2 when column p + 1 was updated ahead by OP_SYRK_COL); K = block p
         const int64_t id = blockIdx.x;
         int64_t aa = (int64_t)((sqrt(8.0 * (double)id + 1.0) - 1.0) * 0.5);
         while (aa * (aa + 1) / 2 > id) --aa;
         while ((aa + 1) * (aa + 2) / 2 <= id) ++aa;
         const int64_t bb = id - aa * (aa + 1) / 2;
-        const int64_t i = p + 1 + aa, j = p + 1 + bb;
+        const int64_t i = q0 + aa, j = q0 + bb;
+        Operand a{As, lda, i * NB, (int64_t)p * NB, n, n};
+        Operand b{As, lda, j * NB, (int64_t)p * NB, n, n};
+        tile_gemm<false>(smem, a, b, NB, acc);
+        tile_store<false>(As, lda, i * NB, j * NB, n, n, -1.0, true, acc);
+    } else if (OP == OP_SYRK_COL) {
+        // look-ahead panel: tile (i, p + 1), i = p + 1 + blockIdx.x; K = block p
+        const int64_t i = p + 1 + blockIdx.x, j = p + 1;
         Operand a{As, lda, i * NB, (int64_t)p * NB, n, n};
         Operand b{As, lda, j * NB, (int64_t)p * NB, n, n};
         tile_gemm<false>(smem, a, b, NB, acc);
@@ -233,12 +242,87 @@ static int set_attrs_once() {
     GPX_SET(diag_kernel, DIAG_SMEM);
     GPX_SET(tile_kernel<OP_SYRK_LEFT>, T_SMEM_BYTES);
     GPX_SET(tile_kernel<OP_SYRK_RIGHT>, T_SMEM_BYTES);
+    GPX_SET(tile_kernel<OP_SYRK_COL>, T_SMEM_BYTES);
     GPX_SET(tile_kernel<OP_TRSM>, T_SMEM_BYTES);
     GPX_SET(tile_kernel<OP_TRTRI_ACC>, T_SMEM_BYTES);
     GPX_SET(tile_kernel<OP_TRTRI_FIN>, T_SMEM_BYTES);
     GPX_SET(tile_kernel<OP_TRTRI_RIGHT>, T_SMEM_BYTES);
 #undef GPX_SET
     done = 1;
+    return 0;
+}
+
+// High-priority side stream of the calling thread's current device (created once per device).
+static cudaStream_t side_stream() {
+    static cudaStream_t streams[64] = {};
+    static std::mutex mu;
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
+    std::lock_guard<std::mutex> lock(mu);
+    if (!streams[dev]) {
+        int lo = 0, hi = 0;
+        cudaDeviceGetStreamPriorityRange(&lo, &hi);      // hi = numerically lowest = greatest priority
+        if (cudaStreamCreateWithPriority(&streams[dev], cudaStreamNonBlocking, hi) != cudaSuccess) {
+            streams[dev] = nullptr;
+            cudaGetLastError();
+        }
+    }
+    return streams[dev];
+}
+
+// Right-looking Cholesky with one block column of look-ahead, for few large matrices (C4:
+// n = 16384, S = 1).  After the TRSM of column p, column p + 1 alone is updated first
+// (OP_SYRK_COL, T-p-1 tiles); its 128x128 diagonal factorisation + inverse (one CTA per matrix,
+// latency-bound) and its TRSM then run on a high-priority side stream while the main stream
+// applies the rank-128 update of step p to the rest of the trailing matrix (columns >= p + 2).
+// Fork / join by events only, so the call stays asynchronous and graph-capturable.
+// Returns 0 / cudaError_t, or -1 when no side stream could be created (nothing enqueued).
+static int potrf_right_lookahead(int64_t S, int64_t n, int T, double *A, int64_t lda, double *dinv,
+                                 int32_t *info, cudaStream_t st) {
+    cudaStream_t ss = side_stream();
+    if (!ss) return -1;
+    cudaEvent_t ev_panel = nullptr, ev_side = nullptr;
+    if (cudaEventCreateWithFlags(&ev_panel, cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&ev_side, cudaEventDisableTiming) != cudaSuccess) {
+        if (ev_panel) cudaEventDestroy(ev_panel);
+        cudaGetLastError();
+        return -1;
+    }
+    auto diag_trsm = [&](int p, cudaStream_t q) {
+        diag_kernel<<<(unsigned)S, 256, DIAG_SMEM, q>>>(n, p, A, lda, dinv, info);
+        count_launches(1);
+        if (p + 1 < T) {
+            dim3 g((unsigned)(T - p - 1), (unsigned)S);
+            tile_kernel<OP_TRSM><<<g, T_THREADS, T_SMEM_BYTES, q>>>(n, p, A, lda, nullptr, 0, dinv, 0);
+            count_launches(1);
+        }
+    };
+    diag_trsm(0, st);
+    for (int p = 0; p + 1 < T; ++p) {
+        {   // column p + 1 first
+            dim3 g((unsigned)(T - p - 1), (unsigned)S);
+            tile_kernel<OP_SYRK_COL><<<g, T_THREADS, T_SMEM_BYTES, st>>>(n, p, A, lda, nullptr, 0, dinv, 0);
+            count_launches(1);
+        }
+        cudaEventRecord(ev_panel, st);
+        cudaStreamWaitEvent(ss, ev_panel, 0);
+        diag_trsm(p + 1, ss);
+        cudaEventRecord(ev_side, ss);
+        if (p + 2 < T) {   // rest of the rank-128 update of step p, concurrently with the side stream
+            const int64_t tr = T - p - 2;
+            dim3 g2((unsigned)(tr * (tr + 1) / 2), (unsigned)S);
+            tile_kernel<OP_SYRK_RIGHT><<<g2, T_THREADS, T_SMEM_BYTES, st>>>(n, p, A, lda, nullptr, 0, dinv, p + 2);
+            count_launches(1);
+        }
+        cudaStreamWaitEvent(st, ev_side, 0);     // join: step p + 1 needs column p + 1 solved
+    }
+    cudaEventDestroy(ev_panel);                  // released once the pending work has used them
+    cudaEventDestroy(ev_side);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) {
+        set_error("gpx_potrf_batched: CUDA error %d (%s)", (int)e, cudaGetErrorString(e));
+        return (int)e;
+    }
     return 0;
 }
 
@@ -265,22 +349,26 @@ extern "C" int gpx_potrf_batched(int64_t S, int64_t n, double *A, int64_t lda, d
     const int T = (int)((n + NB - 1) / NB);
     // schedule: left-looking when the batch alone fills the machine
     const bool left = (S * (int64_t)((T + 1) / 2) >= 296);
+    if (!left && T >= 4) {
+        rc = potrf_right_lookahead(S, n, T, A, lda, dinv, info, st);
+        if (rc >= 0) return rc;     // < 0: side stream unavailable, fall through to the plain schedule
+    }
     for (int p = 0; p < T; ++p) {
         if (left && p > 0) {
             dim3 g((unsigned)(T - p), (unsigned)S);
-            tile_kernel<OP_SYRK_LEFT><<<g, T_THREADS, T_SMEM_BYTES, st>>>(n, p, A, lda, nullptr, 0, dinv);
+            tile_kernel<OP_SYRK_LEFT><<<g, T_THREADS, T_SMEM_BYTES, st>>>(n, p, A, lda, nullptr, 0, dinv, 0);
             count_launches(1);
         }
         diag_kernel<<<(unsigned)S, 256, DIAG_SMEM, st>>>(n, p, A, lda, dinv, info);
         count_launches(1);
         if (p + 1 < T) {
             dim3 g((unsigned)(T - p - 1), (unsigned)S);
-            tile_kernel<OP_TRSM><<<g, T_THREADS, T_SMEM_BYTES, st>>>(n, p, A, lda, nullptr, 0, dinv);
+            tile_kernel<OP_TRSM><<<g, T_THREADS, T_SMEM_BYTES, st>>>(n, p, A, lda, nullptr, 0, dinv, 0);
             count_launches(1);
             if (!left) {
                 int64_t tr = T - p - 1;
                 dim3 g2((unsigned)(tr * (tr + 1) / 2), (unsigned)S);
-                tile_kernel<OP_SYRK_RIGHT><<<g2, T_THREADS, T_SMEM_BYTES, st>>>(n, p, A, lda, nullptr, 0, dinv);
+                tile_kernel<OP_SYRK_RIGHT><<<g2, T_THREADS, T_SMEM_BYTES, st>>>(n, p, A, lda, nullptr, 0, dinv, p + 1);
                 count_launches(1);
             }
         }
@@ -318,15 +406,15 @@ extern "C" int gpx_trtri_batched(int64_t S, int64_t n, const double *L, int64_t 
         if (p > 0) {
             dim3 g((unsigned)p, (unsigned)S);
             if (left) {
-                tile_kernel<OP_TRTRI_ACC><<<g, T_THREADS, T_SMEM_BYTES, st>>>(n, p, W, ldw, L, ldl, dinv);
+                tile_kernel<OP_TRTRI_ACC><<<g, T_THREADS, T_SMEM_BYTES, st>>>(n, p, W, ldw, L, ldl, dinv, 0);
                 count_launches(1);
             }
-            tile_kernel<OP_TRTRI_FIN><<<g, T_THREADS, T_SMEM_BYTES, st>>>(n, p, W, ldw, L, ldl, dinv);
+            tile_kernel<OP_TRTRI_FIN><<<g, T_THREADS, T_SMEM_BYTES, st>>>(n, p, W, ldw, L, ldl, dinv, 0);
             count_launches(1);
         }
         if (!left && p + 1 < T) {
             dim3 g((unsigned)((int64_t)(T - p - 1) * (p + 1)), (unsigned)S);
-            tile_kernel<OP_TRTRI_RIGHT><<<g, T_THREADS, T_SMEM_BYTES, st>>>(n, p, W, ldw, L, ldl, dinv);
+            tile_kernel<OP_TRTRI_RIGHT><<<g, T_THREADS, T_SMEM_BYTES, st>>>(n, p, W, ldw, L, ldl, dinv, 0);
             count_launches(1);
         }
     }
