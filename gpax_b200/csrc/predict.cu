@@ -73,6 +73,19 @@ __host__ __device__ constexpr int dmax_of(int d) { return d <= 2 ? 2 : (d <= 4 ?
 // 3 FP64 instructions per dimension on the pipe the DMMAs need, instead of ~100.  The absolute
 // error of each sine stays at the 1e-16 level of the reference's own sin(pi * diff / period).
 constexpr int GPX_PERIODIC_FEAT = 3;
+// sin and cos of pi * x / p with the quotient carried in double-double and reduced mod 2
+// exactly, so the angle error is ~1e-16 absolute whatever |x / p| is (a plain
+// sincos(pi * x / p) loses |x/p| ulps, which the ill-conditioned solves then amplify)
+__device__ __forceinline__ void sincos_pi_ratio(double x, double p, double &sn, double &cs) {
+    const double hi = x / p;
+    const double lo = fma(-hi, p, x) / p;
+    const double r = hi - 2.0 * rint(0.5 * hi);
+    double s0, c0;
+    sincospi(r, &s0, &c0);
+    const double t = GPX_PI * lo;
+    sn = fma(c0, t, s0);
+    cs = fma(-s0, t, c0);
+}
 __host__ __device__ constexpr int feat_dim(int kind, int d) { return kind == GPX_PERIODIC_FEAT ? 2 * d : d; }
 
 // ---- mbarrier / TMA / shared-memory primitives (PTX) -------------------------
@@ -142,7 +155,7 @@ predict_prep_kernel(gpx_kernel_params kp, int n, int n_pad, const double *__rest
     if (KIND == GPX_PERIODIC_FEAT) {
         for (int q = 0; q < d; ++q) {
             double sn, cs;
-            sincos(GPX_PI * x[(size_t)k * d + q] / per_of(kp, s, q), &sn, &cs);
+            sincos_pi_ratio(x[(size_t)k * d + q], per_of(kp, s, q), sn, cs);
             const double l = len_of(kp, s, q);
             dst[2 * q] = sn / l;
             dst[2 * q + 1] = cs / l;
@@ -297,7 +310,7 @@ predict_ws_kernel(const __grid_constant__ CUtensorMap tmW, gpx_kernel_params kp,
         if (KIND == GPX_PERIODIC_FEAT) {
             for (int q = 0; q < GPX_MAX_D / 2; ++q) {
                 double sn = 0.0, cs = 0.0;
-                if (gj < M && q < d) sincos(GPX_PI * xnew[(size_t)gj * d + q] / s_per[q], &sn, &cs);
+                if (gj < M && q < d) sincos_pi_ratio(xnew[(size_t)gj * d + q], s_per[q], sn, cs);
                 sZ[e * (GPX_MAX_D + 1) + 2 * q] = cs;
                 sZ[e * (GPX_MAX_D + 1) + 2 * q + 1] = -sn;
             }
@@ -668,14 +681,11 @@ static int launch_predict_ws_d(const gpx_kernel_params *kp, int64_t S, int64_t n
                                const double *xs, const double *xnew, const double *W, int64_t ldw,
                                const double *m_new, double m_const, const double *diag_add,
                                double *mu, double *var, int64_t ldo, int64_t ldmn, cudaStream_t st) {
-    if constexpr (KIND == GPX_PERIODIC)   // sin path: only d > 4 gets here (see dispatch_predict)
-        return launch_predict_ws<KIND, WN, 8>(kp, S, n, M, xs, xnew, W, ldw, m_new, m_const, diag_add, mu, var, ldo, ldmn, st);
-    else
-        switch (dmax_of(feat_dim(KIND, kp->d))) {
-            case 2: return launch_predict_ws<KIND, WN, 2>(kp, S, n, M, xs, xnew, W, ldw, m_new, m_const, diag_add, mu, var, ldo, ldmn, st);
-            case 4: return launch_predict_ws<KIND, WN, 4>(kp, S, n, M, xs, xnew, W, ldw, m_new, m_const, diag_add, mu, var, ldo, ldmn, st);
-            default: return launch_predict_ws<KIND, WN, 8>(kp, S, n, M, xs, xnew, W, ldw, m_new, m_const, diag_add, mu, var, ldo, ldmn, st);
-        }
+    switch (dmax_of(feat_dim(KIND, kp->d))) {
+        case 2: return launch_predict_ws<KIND, WN, 2>(kp, S, n, M, xs, xnew, W, ldw, m_new, m_const, diag_add, mu, var, ldo, ldmn, st);
+        case 4: return launch_predict_ws<KIND, WN, 4>(kp, S, n, M, xs, xnew, W, ldw, m_new, m_const, diag_add, mu, var, ldo, ldmn, st);
+        default: return launch_predict_ws<KIND, WN, 8>(kp, S, n, M, xs, xnew, W, ldw, m_new, m_const, diag_add, mu, var, ldo, ldmn, st);
+    }
 }
 
 template <int KIND>
@@ -694,7 +704,10 @@ static int dispatch_predict(const gpx_kernel_params *kp, int64_t S, int64_t n, i
     dim3 g((unsigned)((n_pad + 255) / 256), (unsigned)S);
     // Periodic with d <= 4 runs on angle-addition features (GPX_PERIODIC_FEAT above)
     constexpr int KF = (KIND == GPX_PERIODIC) ? GPX_PERIODIC_FEAT : KIND;
-    const bool feat = (KIND == GPX_PERIODIC) && kp->d <= GPX_MAX_D / 2;
+    // GPX_PERIODIC_SINE=1 forces the per-pair sine (accuracy comparisons only)
+    static int force_sine = -1;
+    if (force_sine < 0) { const char *e = getenv("GPX_PERIODIC_SINE"); force_sine = (e && atoi(e)) ? 1 : 0; }
+    const bool feat = (KIND == GPX_PERIODIC) && kp->d <= GPX_MAX_D / 2 && !force_sine;
     if (prep) {   // per-sample scaled training inputs: once per (x, theta), not per candidate tile
         if (feat) predict_prep_kernel<KF><<<g, 256, 0, st>>>(*kp, (int)n, n_pad, x, alpha, ws);
         else predict_prep_kernel<KIND><<<g, 256, 0, st>>>(*kp, (int)n, n_pad, x, alpha, ws);

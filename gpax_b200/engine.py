@@ -279,7 +279,7 @@ class Posterior:
 
     def predict(self, x_new, m_new=None, m_const=1.0, observation_noise=False,
                 want_mu=True, want_var=True):
-        xn = _dev(np.asarray(x_new, float).reshape(len(x_new), -1), self.dev) \
+        xn = _dev(np.asarray(x_new, float).reshape(len(x_new), self.d), self.dev) \
             if not isinstance(x_new, torch.Tensor) else x_new
         diag_add = (self.hpd.noise + self.hpd.jitter) if observation_noise else self.hpd.jitter
         mn = _dev(m_new, self.dev) if m_new is not None else None
@@ -289,7 +289,7 @@ class Posterior:
     def predict_acq(self, x_new, acq, beta=10.0, y_max=0.0, mu_scale=1.0, mu_shift=0.0,
                     sd_scale=1.0, m_offset=0, m_new=None, m_const=1.0, observation_noise=False,
                     m_tile=None, want_arrays=True):
-        xn = _dev(np.asarray(x_new, float).reshape(len(x_new), -1), self.dev) \
+        xn = _dev(np.asarray(x_new, float).reshape(len(x_new), self.d), self.dev) \
             if not isinstance(x_new, torch.Tensor) else x_new
         diag_add = (self.hpd.noise + self.hpd.jitter) if observation_noise else self.hpd.jitter
         mn = _dev(m_new, self.dev) if m_new is not None else None
