@@ -69,12 +69,17 @@ gram_kernel(gpx_kernel_params kp, int64_t n, int64_t m, const double *__restrict
 #pragma unroll
         for (int c = 0; c < 4; ++c) {
             const int lj = tx * 4 + c;
-            if (KIND == GPX_PERIODIC) {
+            if (KIND == GPX_PERIODIC)
                 v[c] = k_periodic(p1[li], p2[lj], s_per, s_len, d, scale);
-            } else {
-                double r2 = r2_expansion(p1[li], p1[li][GPX_MAX_D], p2[lj], p2[lj][GPX_MAX_D], d);
-                v[c] = k_from_r2<KIND>(r2, scale);
-            }
+            else
+                v[c] = r2_expansion(p1[li], p1[li][GPX_MAX_D], p2[lj], p2[lj][GPX_MAX_D], d);
+        }
+        // branch-free 4-wide exp / sqrt (common.cuh): same formulas as k_from_r2, <= 1 ulp apart,
+        // about half the instructions of four libm calls (the kernel is issue-bound, not HBM-bound)
+        if (KIND != GPX_PERIODIC) k_from_r2_vec<KIND == GPX_PERIODIC ? GPX_RBF : KIND, 4>(v, scale);
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+            const int lj = tx * 4 + c;
             const int64_t gj = j0 + lj;
             if (add_diag && gi == gj) {
                 double nz = 0.0;

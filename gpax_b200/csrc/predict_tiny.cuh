@@ -145,40 +145,44 @@ predict_tiny_kernel(gpx_kernel_params kp, int n, int M, int cand_per_cta,
                 // ---- generate K*^T slice c: k = 16c .. 16c+15 for this lane's candidate ----
 #pragma unroll
                 for (int g = 0; g < T_BK; g += 4) {
-                    double v[4];
+                    const int k0 = c * T_BK + g;
+                    double v[4], al[4];
+                    // staged rows are SoA and 16-byte aligned: one LDS.128 serves two k
+                    lds128(al[0], al[1], sX + (GPX_MAX_D + 1) * T_N + k0);
+                    lds128(al[2], al[3], sX + (GPX_MAX_D + 1) * T_N + k0 + 2);
+                    if (KIND == GPX_PERIODIC) {
 #pragma unroll
-                    for (int i = 0; i < 4; ++i) {
-                        const int k = c * T_BK + g + i;
-                        if (KIND == GPX_PERIODIC) {
+                        for (int i = 0; i < 4; ++i) {
                             double a2 = 0.0;
 #pragma unroll
                             for (int q = 0; q < DMAX; ++q)
                                 if (q < d) {
-                                    double df = z[q] - sX[q * T_N + k];
+                                    double df = z[q] - sX[q * T_N + k0 + i];
                                     double sn = sin(GPX_PI * df / s_per[q]) / s_len[q];
                                     a2 += sn * sn;
                                 }
-                            v[i] = a2;
-                        } else {
-                            double xz = 0.0;
-#pragma unroll
-                            for (int q = 0; q < DMAX; ++q)
-                                if (q < d) xz = fma(z[q], sX[q * T_N + k], xz);
-                            v[i] = fmax((zn - 2.0 * xz) + sX[GPX_MAX_D * T_N + k], 0.0);
+                            v[i] = scale * exp(-2.0 * a2);
                         }
-                    }
-                    if (KIND == GPX_PERIODIC) {
-#pragma unroll
-                        for (int i = 0; i < 4; ++i) v[i] = scale * exp(-2.0 * v[i]);
                     } else {
+                        double xz[4] = {0.0, 0.0, 0.0, 0.0}, xn[4];
+#pragma unroll
+                        for (int q = 0; q < DMAX; ++q)
+                            if (q < d) {
+                                double xq[4];
+                                lds128(xq[0], xq[1], sX + q * T_N + k0);
+                                lds128(xq[2], xq[3], sX + q * T_N + k0 + 2);
+#pragma unroll
+                                for (int i = 0; i < 4; ++i) xz[i] = fma(z[q], xq[i], xz[i]);
+                            }
+                        lds128(xn[0], xn[1], sX + GPX_MAX_D * T_N + k0);
+                        lds128(xn[2], xn[3], sX + GPX_MAX_D * T_N + k0 + 2);
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) v[i] = fmax((zn - 2.0 * xz[i]) + xn[i], 0.0);
                         k_from_r2_vec<KIND == GPX_PERIODIC ? GPX_RBF : KIND, 4>(v, scale);
                     }
+                    // k >= n: W's columns and alpha are zero there, so the (finite) values are inert
 #pragma unroll
-                    for (int i = 0; i < 4; ++i) {
-                        const int k = c * T_BK + g + i;
-                        v[i] = (k < n) ? v[i] : 0.0;
-                        macc = fma(v[i], sX[(GPX_MAX_D + 1) * T_N + k], macc);
-                    }
+                    for (int i = 0; i < 4; ++i) macc = fma(v[i], al[i], macc);
                     sts128(sK + lane * T_LD + g, v[0], v[1]);
                     sts128(sK + lane * T_LD + g + 2, v[2], v[3]);
                 }
