@@ -44,6 +44,11 @@ constexpr int W_BK = 16;                       // 128-byte rows = one swizzle sp
 constexpr int W_GEN_AHEAD = 2;                 // K* slices are generated this many slices ahead
 constexpr int W_NK = 5;                        // K* ring slots (>= GEN_AHEAD + 2: no "empty" barrier needed)
 constexpr int W_MF = 8, W_NF = 4;              // per-warp fragment grid: 64 rows x 32 candidates
+constexpr int W_NX = 4;                        // staged-training-row ring slots (>= GEN_AHEAD + 2, like W_NK)
+// shared memory of predict_ws_kernel<KIND, WN, DMAX>: WCfg<WN>::SMEM_BYTES + the row ring + its barriers
+__host__ __device__ constexpr size_t xring_bytes(int dmax) {
+    return (size_t)W_NX * W_BK * (dmax + 2) * sizeof(double) + W_NX * sizeof(uint64_t);
+}
 
 template <int WN>
 struct WCfg {
@@ -120,6 +125,13 @@ __device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap *tm,
         : "memory");
 }
 // 16-byte shared load at a 32-bit shared address (+ compile-time byte offset -> LDS.128 [R+imm])
+// 1-D bulk async copy global -> shared (TMA engine, no tensor map), completing on an mbarrier
+__device__ __forceinline__ void bulk_load(uint32_t smem_dst, const void *gsrc, uint32_t bytes, uint32_t bar) {
+    asm volatile(
+        "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];\n" ::"r"(smem_dst),
+        "l"(gsrc), "r"(bytes), "r"(bar)
+        : "memory");
+}
 __device__ __forceinline__ double2 lds128(uint32_t addr) {
     double2 v;
     asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];\n" : "=d"(v.x), "=d"(v.y) : "r"(addr));
@@ -275,7 +287,8 @@ predict_ws_kernel(const __grid_constant__ CUtensorMap tmW, gpx_kernel_params kp,
     double *smean = wpart + WM * C::MT;                   // [GEN][W_THREADS]
     double *s_len = smean + W_THREADS * C::GEN;           // [MAX_D]
     double *s_per = s_len + GPX_MAX_D;                    // [MAX_D]
-    uint64_t *bars = reinterpret_cast<uint64_t *>(s_per + GPX_MAX_D);
+    double *sXr = s_per + GPX_MAX_D;                      // [W_NX][W_BK][XSP] staged training rows (16-byte aligned)
+    uint64_t *bars = reinterpret_cast<uint64_t *>(sXr + W_NX * W_BK * XSP);
 
     const int s = blockIdx.y;
     const int j0 = blockIdx.x * C::MT;
@@ -283,7 +296,10 @@ predict_ws_kernel(const __grid_constant__ CUtensorMap tmW, gpx_kernel_params kp,
     const int d = kp.d;
     const double scale = kp.scale[s];
     const uint32_t bar_fullW = smem_u32(bars), bar_emptyW = bar_fullW + 8 * C::NST,
-                   bar_fullK = bar_emptyW + 8 * C::NST;
+                   bar_fullK = bar_emptyW + 8 * C::NST, bar_fullX = bar_fullK + 8 * W_NK;
+    constexpr uint32_t X_BYTES = W_BK * XSP * sizeof(double);      // one slice of staged rows
+    const double *xs_s = xs + (size_t)s * n_pad * XSP;
+    const uint32_t sXr_u = smem_u32(sXr);
 
     if (t < GPX_MAX_D) {
         s_len[t] = t < d ? len_of(kp, s, t) : 1.0;
@@ -298,6 +314,8 @@ predict_ws_kernel(const __grid_constant__ CUtensorMap tmW, gpx_kernel_params kp,
         }
 #pragma unroll
         for (int i = 0; i < W_NK; ++i) mbar_init(bar_fullK + 8 * i, W_WARPS);
+#pragma unroll
+        for (int i = 0; i < W_NX; ++i) mbar_init(bar_fullX + 8 * i, 1);
         asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
         asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory");
         asm volatile("prefetch.tensormap [%0];\n" ::"l"(&tmW) : "memory");
@@ -361,21 +379,25 @@ predict_ws_kernel(const __grid_constant__ CUtensorMap tmW, gpx_kernel_params kp,
         const int col = jb + 16 * i;
         offK[i] = (uint32_t)(col * W_BK + (((gk >> 1) ^ (col & 7)) << 1) + (gk & 1)) * 8u;
     }
-    // staged training row (coords, norm, alpha) of the slice being generated, fetched one slice ahead
-    const double2 *xrow0 = reinterpret_cast<const double2 *>(xs + ((size_t)s * n_pad + gk) * XSP);
-    const double2 *xrow = xrow0;
-    double2 xr[XSP / 2];
-#pragma unroll
-    for (int q = 0; q < XSP / 2; ++q) xr[q] = __ldg(xrow + q);
+    // Staged training rows (coords, norm, alpha) of the slice being generated come from the
+    // shared row ring: the elected TMA thread bulk-copies the 16 rows of slice gi + 1 while slice
+    // gi is generated, so no thread holds a prefetched row in registers across the DMMA block
+    // (the register copy of that prefetch was the largest single stall of the r01 kernel).
+    const uint32_t xrow_u = sXr_u + (uint32_t)(gk * XSP) * 8u;
     int gi = 0, g_rb = 0, g_c = 0, g_nsl = nsl_of(0);     // next slice to generate
     uint32_t gslot = 0;                                   // its K* ring slot
     double macc[GEN];
 #pragma unroll
     for (int i = 0; i < GEN; ++i) macc[i] = 0.0;
 
-    auto xr_at = [&](int q) { return (q & 1) ? xr[q >> 1].y : xr[q >> 1].x; };
-    // gen_begin: distances of this thread's GEN entries of slice gi (registers only)
+    // gen_begin: distances of this thread's GEN entries of slice gi
     auto gen_begin = [&](Gen &g, double &al) {
+        double2 xr[XSP / 2];
+        mbar_wait(bar_fullX + 8 * (gi & (W_NX - 1)), (gi / W_NX) & 1);
+#pragma unroll
+        for (int q = 0; q < XSP / 2; ++q)
+            xr[q] = lds128(xrow_u + (uint32_t)(gi & (W_NX - 1)) * X_BYTES + q * 16);
+        auto xr_at = [&](int q) { return (q & 1) ? xr[q >> 1].y : xr[q >> 1].x; };
 #pragma unroll
         for (int i = 0; i < GEN; ++i) {
             double zq[DMAX + 1];
@@ -414,16 +436,18 @@ predict_ws_kernel(const __grid_constant__ CUtensorMap tmW, gpx_kernel_params kp,
         }
         al = xr_at(DMAX + 1);
     };
-    // fetch the row of the next slice to generate (first slice of the next row block after
-    // the last); issued right before the DMMA block, which covers the load latency
-    auto gen_prefetch = [&]() {
-        xrow = (g_c + 1 < g_nsl) ? xrow + (W_BK * XSP / 2) : xrow0;
-#pragma unroll
-        for (int q = 0; q < XSP / 2; ++q) xr[q] = __ldg(xrow + q);
+    // x_issue (the elected TMA thread): rows of slice g (k offset c16 * 16) -> ring slot g % W_NX.
+    // The slot last held slice g - W_NX, whose readers all passed before the fullK barrier that
+    // the issuing thread has already waited on (same argument as for the K* ring below).
+    auto x_issue = [&](int g, int c16) {
+        const uint32_t xb = bar_fullX + 8 * (g & (W_NX - 1));
+        mbar_arrive_expect_tx(xb, X_BYTES);
+        bulk_load(sXr_u + (uint32_t)(g & (W_NX - 1)) * X_BYTES, xs_s + (size_t)c16 * W_BK * XSP, X_BYTES, xb);
     };
     // tma_issue (one elected thread): as soon as the stage of slice gi is released,
     // stream the W slab of that slice into it -- two slices ahead of its use
     auto tma_issue = [&]() {
+        if (gi + 1 < T) x_issue(gi + 1, (g_c + 1 < g_nsl) ? g_c + 1 : 0);
         const uint32_t gst = gi % C::NST, gph = (gi / C::NST) & 1;
         mbar_wait(bar_emptyW + 8 * gst, gph ^ 1);
         if (DBG & 4) {
@@ -456,12 +480,12 @@ predict_ws_kernel(const __grid_constant__ CUtensorMap tmW, gpx_kernel_params kp,
         }
     };
     // prologue: the first D slices
+    if (warp == 0 && elect_one()) x_issue(0, 0);
     for (int q = 0; q < D && gi < T; ++q) {
         Gen g;
         double al;
         if (warp == 0 && elect_one()) tma_issue();
         gen_begin(g, al);
-        gen_prefetch();
         if (!(DBG & 1)) g.template run<0, NS>(scale);
         gen_end(g, al);
     }
@@ -501,7 +525,6 @@ predict_ws_kernel(const __grid_constant__ CUtensorMap tmW, gpx_kernel_params kp,
             if (has_g) {
                 if (warp == 0 && elect_one()) tma_issue();
                 gen_begin(g, al);
-                gen_prefetch();
             }
             mbar_wait(bar_fullW + 8 * st, ph);
             mbar_wait(bar_fullK + 8 * slot, kph);
@@ -647,7 +670,7 @@ static int launch_predict_ws(const gpx_kernel_params *kp, int64_t S, int64_t n, 
     if (!configured) {
         cudaError_t e = cudaFuncSetAttribute(predict_ws_kernel<KIND, WN, DMAX>,
                                              cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                             (int)C::SMEM_BYTES);
+                                             (int)(C::SMEM_BYTES + xring_bytes(DMAX)));
         if (e != cudaSuccess) { set_error("gpx_predict: smem attribute failed (%d)", (int)e); return (int)e; }
         configured = true;
     }
@@ -663,15 +686,15 @@ static int launch_predict_ws(const gpx_kernel_params *kp, int64_t S, int64_t n, 
 #define GPX_DBG_CASE(D)                                                                            \
         case D: {                                                                                  \
             static bool cfg = false;                                                               \
-            if (!cfg) { cudaFuncSetAttribute(predict_ws_kernel<GPX_MATERN52, 1, 2, D>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::SMEM_BYTES); cfg = true; } \
-            predict_ws_kernel<GPX_MATERN52, 1, 2, D><<<grid, W_THREADS, C::SMEM_BYTES, st>>>(      \
+            if (!cfg) { cudaFuncSetAttribute(predict_ws_kernel<GPX_MATERN52, 1, 2, D>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(C::SMEM_BYTES + xring_bytes(2))); cfg = true; } \
+            predict_ws_kernel<GPX_MATERN52, 1, 2, D><<<grid, W_THREADS, C::SMEM_BYTES + xring_bytes(2), st>>>(      \
                 tm, *kp, (int)n, n_pad, (int)M, xs, xnew, m_new, m_const, diag_add, mu, var, ldo, ldmn);      \
             return 0; }
         switch (dbg) { GPX_DBG_CASE(1) GPX_DBG_CASE(2) GPX_DBG_CASE(3) default: break; }
 #undef GPX_DBG_CASE
     }
 #endif
-    predict_ws_kernel<KIND, WN, DMAX><<<grid, W_THREADS, C::SMEM_BYTES, st>>>(
+    predict_ws_kernel<KIND, WN, DMAX><<<grid, W_THREADS, C::SMEM_BYTES + xring_bytes(DMAX), st>>>(
         tm, *kp, (int)n, n_pad, (int)M, xs, xnew, m_new, m_const, diag_add, mu, var, ldo, ldmn);
     return 0;
 }
