@@ -550,3 +550,46 @@ def test_empty_inputs_are_noops(cuda):
     assert out[0].numel() == 0
     assert _cabi.lib.gpx_launch_count() == before
     torch.cuda.synchronize()
+
+
+def test_hot_path_is_cuda_graph_capturable(cuda):
+    """Every entry point only enqueues on the caller's stream (include/gpax_b200.h), so the whole
+    step -- including the look-ahead Cholesky's fork / join onto the library's side stream -- can be
+    captured once and replayed: results must be bit-identical to the eager calls."""
+    import torch
+    from gpax_b200 import engine as E, _cabi
+    n, d, S, M = 600, 2, 2, 300                  # T = 5 blocks, S small -> right-looking + look-ahead
+    x, y, xn, hp = _mk("matern52", n, d, S, M, 4242)
+    hpd = E.HyperParams("matern52", d, hp, cuda)
+    xd, xnd, resid = E._dev(x, cuda), E._dev(xn, cuda), E._dev(y - 1.0, cuda)
+    mt = _cabi.lib.gpx_predict_acq_tile(S, M)
+
+    def step(L, W, dinv, info, ws, mws):
+        E.gram(hpd, xd, xd, add_diag=True, region=_cabi.LOWER, out=L)
+        E.potrf(L, n, dinv, info)
+        val, alpha = E.mll(L, n, dinv, resid, ws=mws)
+        E.trtri(L, n, dinv, W)
+        o = E.predict_acq(hpd, xd, xnd, W, alpha, hpd.jitter, _cabi.ACQ_UCB, 10.0, 0.0, m_tile=mt, ws=ws)
+        return val, o
+
+    def bufs():
+        L = torch.empty((S, n, E.even(n)), dtype=torch.float64, device=cuda)
+        ws = torch.empty(max(1, _cabi.lib.gpx_predict_acq_ws_bytes(S, n, d, mt) // 8), dtype=torch.float64, device=cuda)
+        mws = torch.empty(max(1, _cabi.lib.gpx_mll_ws_bytes(S, n) // 8), dtype=torch.float64, device=cuda)
+        return (L, torch.empty_like(L), E.dinv_alloc(S, n, cuda), torch.zeros(S, dtype=torch.int32, device=cuda), ws, mws)
+
+    val_e, out_e = step(*bufs())                 # eager (also performs the one-time attribute setup)
+    torch.cuda.synchronize()
+    side = torch.cuda.Stream()
+    b = bufs()
+    with torch.cuda.stream(side):
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g, stream=side):
+            val_g, out_g = step(*b)
+    torch.cuda.synchronize()
+    for _ in range(2):
+        g.replay()
+    torch.cuda.synchronize()
+    assert torch.equal(val_g, val_e)
+    for a, e in zip(out_g, out_e):
+        assert torch.equal(a, e)
