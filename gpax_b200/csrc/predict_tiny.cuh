@@ -16,7 +16,8 @@
 //     mean k*.alpha in the same pass, into a warp-private k-contiguous tile;
 //   * the tile is the B operand of DMMAs against W (A operand) with the k-permuted
 //     fragment layout (a lane's four k of a slice are two LDS.128), row fragments
-//     skipped at compile time where W is structurally zero (20 of 32 fragment-slices);
+//     skipped at compile time where W is structurally zero (12 of 32 fragment-slices, and half
+//     of the k-steps of the 4 fragment-slices that contain the diagonal);
 //   * column sums of squares are reduced with shuffles; mu/var stores are 256-byte
 //     coalesced.  No __syncthreads after the prologue, only __syncwarp.
 #pragma once
@@ -195,8 +196,20 @@ predict_tiny_kernel(gpx_kernel_params kp, int n, int M, int cand_per_cta,
                     lds128(b[ni][0], b[ni][1], pb);
                     lds128(b[ni][2], b[ni][3], pb + 2);
                 }
+                {   // fragment 2c (rows 16c .. 16c+7) meets the diagonal inside this slice: only its
+                    // first 8 k are non-zero, so it takes two natural-order k-steps (k = 4 ks + lc,
+                    // plain 8-byte loads) instead of the four permuted ones -- 8 DMMAs saved per slice
+                    constexpr int mi = 2 * c;
 #pragma unroll
-                for (int mi = 2 * c; mi < 8; ++mi) {
+                    for (int ks = 0; ks < 2; ++ks) {
+                        const double a1 = sW[(c * T_N + mi * 8 + lr) * T_LD + ks * 4 + lc];
+#pragma unroll
+                        for (int ni = 0; ni < 4; ++ni)
+                            dmma884(acc[mi][ni][0], acc[mi][ni][1], a1, sK[(ni * 8 + lr) * T_LD + ks * 4 + lc]);
+                    }
+                }
+#pragma unroll
+                for (int mi = 2 * c + 1; mi < 8; ++mi) {
                     double a[4];
                     const double *pa = sW + (c * T_N + mi * 8 + lr) * T_LD + lc * 4;
                     lds128(a[0], a[1], pa);
