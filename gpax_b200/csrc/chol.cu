@@ -102,7 +102,8 @@ diag_kernel(int64_t n, int p, double *__restrict__ A, int64_t lda, double *__res
     // in-place inverse of the lower-triangular block, last column first
     // (column j of X from the already inverted trailing block):
     //   X[j][j] = 1/L[j][j];  X[i][j] = -X[j][j] * sum_{k=j+1..i} X[i][k] L[k][j]
-    for (int j = NB - 1; j >= 0; --j) {
+    // (columns >= nbe belong to the identity padding, which is its own inverse)
+    for (int j = nbe - 1; j >= 0; --j) {
         if (t < NB && t >= j) col[t] = a[fold_base(t) + fold_step(t) * j];
         __syncthreads();
         double xjj = 1.0 / col[j];
