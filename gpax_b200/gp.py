@@ -244,7 +244,7 @@ class GaussianProcess:
 
     def _draw(self, rng_seed, x_new_t, hp, mu, post):
         """Joint draws ``y [S, G, M]`` from ``N(mu_s, cov_s)`` (gpax/gp.py:332-338).
-        Row N1: assembled with library GEMM/Cholesky on the device, not hand-written."""
+        Row N1: covariance assembled with library GEMMs on the device, factorised by gpx_potrf_batched."""
         import torch
 
         from . import _cabi
@@ -272,7 +272,16 @@ class GaussianProcess:
                 W = torch.tril(post.W[sl, :, : post.n])
                 V = torch.bmm(W, kx)
                 cov = cov - torch.bmm(V.transpose(1, 2), V)
-            Lc = torch.linalg.cholesky(cov)
+            # factor of the posterior covariance with the library's own batched blocked Cholesky
+            # (gpx_potrf_batched, lower triangle in place; leading dimension must be even)
+            ldc = M + (M & 1)
+            fac = torch.zeros((cov.shape[0], M, ldc), dtype=torch.float64, device=dev)
+            fac[:, :, :M] = cov
+            _, info = E.potrf(fac, M)
+            if int(info.abs().max()) != 0:
+                raise ValueError("posterior covariance at x_new is not positive definite "
+                                 "(add observation noise or jitter, or use fewer / more distinct points)")
+            Lc = torch.tril(fac[:, :, :M])
             z = torch.randn((Lc.shape[0], M, G), dtype=torch.float64, device=dev, generator=gen)
             y[sl] = mu[sl, None, :] + torch.bmm(Lc, z).transpose(1, 2)
         return y
