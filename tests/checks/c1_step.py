@@ -2,9 +2,9 @@
 step -- Gram -> Cholesky -> MLL/alpha -> L^-1 -> fused predictive + EI argmax -- timed three ways:
 eager C-ABI calls, the same calls captured once in a CUDA graph and replayed (the step is launch-bound
 at this size; every gpx_* entry point only enqueues, so the sequence is capturable), and the CPU oracle
-on the host cores.  python tools/c1_step.py [reps]"""
+on the host cores.  python tests/checks/c1_step.py [reps]"""
 import os, sys, time
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
 import numpy as np, torch
 from gpax_b200 import engine as E, synthetic as syn, _cabi
 from oracle import gp_oracle as O

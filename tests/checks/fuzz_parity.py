@@ -1,9 +1,9 @@
 """Randomised parity sweep (GPU vs CPU oracle) over ragged shapes of every predictive / acquisition
 kernel variant: kind x n in [1, 700] x d in [1, 8] x S in [1, 6] x M in [1, 900], with / without a
 custom mean, observation noise, ARD length scales.  Prints one line per failure and a summary; exit
-code 1 on any failure.  python tools/fuzz_parity.py [cases] [seed]"""
+code 1 on any failure.  python tests/checks/fuzz_parity.py [cases] [seed]"""
 import os, sys
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
 import numpy as np, torch
 from gpax_b200 import engine as E, synthetic as syn, _cabi
 from oracle import gp_oracle as O

@@ -1,8 +1,8 @@
 """Accuracy of the Periodic predictive paths (angle-addition features vs per-pair sine; set
 GPX_PERIODIC_SINE=1 for the latter) against the oracle on ill-conditioned 1-D problems, with RBF /
-Matern on the same inputs for scale.  python tools/periodic_accuracy.py"""
+Matern on the same inputs for scale.  python tests/checks/periodic_accuracy.py"""
 import os, sys
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
 import numpy as np, torch
 from gpax_b200 import engine as E, synthetic as syn
 from oracle import gp_oracle as O

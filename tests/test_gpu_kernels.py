@@ -518,7 +518,7 @@ def test_predict_periodic_feature_and_sine_paths(cuda, n, d, tol):
     n <= 128 on the per-pair sine; both must match the reference formula
     (gpax/kernels.py:163-165) at 1e-10.  The last case (700 points on a 1-D interval,
     kappa(K) ~ 1e6) is conditioning-limited: the per-pair sine path itself sits at 5e-11
-    there and the feature path at 1.0e-10 (tools/periodic_accuracy.py), so it is held to
+    there and the feature path at 1.0e-10 (tests/checks/periodic_accuracy.py), so it is held to
     3e-10 and documented in DESIGN.md section 2."""
     import torch
     from gpax_b200 import engine as E
