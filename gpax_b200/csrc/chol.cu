@@ -139,7 +139,7 @@ diag_kernel(int64_t n, int p, double *__restrict__ A, int64_t lda, double *__res
 // tile kernels (one CTA = one 128x128 tile; blockIdx.y = sample)
 // ---------------------------------------------------------------------------
 enum { OP_SYRK_LEFT = 0, OP_SYRK_RIGHT = 1, OP_TRSM = 2, OP_TRTRI_ACC = 3, OP_TRTRI_FIN = 4,
-       OP_TRTRI_RIGHT = 5, OP_SYRK_COL = 6 };
+       OP_TRTRI_RIGHT = 5, OP_SYRK_COL = 6, OP_TRTRI_RIGHT2 = 7 };
 
 template <int OP>
 __global__ void __launch_bounds__(T_THREADS, 1)
@@ -198,6 +198,23 @@ tile_kernel(int64_t n, int p, double *__restrict__ A, int64_t lda, const double 
         Operand b{As, lda, j * NB, j * NB, n, n};
         tile_gemm<true>(smem, a, b, (int64_t)(p - j) * NB, acc);
         tile_store<true>(As, lda, (int64_t)p * NB, j * NB, n, n, 1.0, false, acc);
+    } else if (OP == OP_TRTRI_RIGHT2) {
+        // right-looking double step (p, p+1): W(i, j) (+)= [L(i,p) L(i,p+1)] [W(p,j); W(p+1,j)] for
+        // p + 1 < i < T, 0 <= j <= p (K = 2 NB: rank-256 tiles run closer to the deep-K rate than
+        // rank-128 ones and halve the read-modify-write traffic), and the first term
+        // W(i, p+1) = L(i,p+1) W(p+1,p+1).  blockIdx.x = (i - p - 2) * (p + 2) + j.
+        const int64_t i = p + 2 + blockIdx.x / (p + 2), j = blockIdx.x % (p + 2);
+        if (j <= p) {
+            Operand a{Ls, ldl, i * NB, (int64_t)p * NB, n, n};
+            Operand b{As, lda, (int64_t)p * NB, j * NB, n, n};
+            tile_gemm<true>(smem, a, b, 2 * NB, acc);
+            tile_store<true>(As, lda, i * NB, j * NB, n, n, 1.0, j != p, acc);
+        } else {
+            Operand a{Ls, ldl, i * NB, (int64_t)(p + 1) * NB, n, n};
+            Operand b{As, lda, (int64_t)(p + 1) * NB, (int64_t)(p + 1) * NB, n, n};
+            tile_gemm<true>(smem, a, b, NB, acc);
+            tile_store<true>(As, lda, i * NB, j * NB, n, n, 1.0, false, acc);
+        }
     } else if (OP == OP_TRTRI_RIGHT) {
         // right-looking step p: W(i, j) (+)= L(i,p) W(p,j) for p < i < T, 0 <= j <= p
         // (blockIdx.x = (i - p - 1) * (p + 1) + j; tile (i, p) receives its first term here)
@@ -248,6 +265,7 @@ static int set_attrs_once() {
     GPX_SET(tile_kernel<OP_TRTRI_ACC>, T_SMEM_BYTES);
     GPX_SET(tile_kernel<OP_TRTRI_FIN>, T_SMEM_BYTES);
     GPX_SET(tile_kernel<OP_TRTRI_RIGHT>, T_SMEM_BYTES);
+    GPX_SET(tile_kernel<OP_TRTRI_RIGHT2>, T_SMEM_BYTES);
 #undef GPX_SET
     done = 1;
     return 0;
@@ -403,20 +421,36 @@ extern "C" int gpx_trtri_batched(int64_t S, int64_t n, const double *L, int64_t 
     // RIGHT-looking (rank-NB update of every row below p, (T-p-1)(p+1) tiles per launch)
     // for few large matrices, where a block row alone is less than one wave.
     const bool left = (S * (int64_t)((T + 1) / 2) >= 296);
-    for (int p = 0; p < T; ++p) {
-        if (p > 0) {
+    auto fin = [&](int p) {          // W(p, j) <- -Dinv(p) W(p, j), j < p
+        if (p == 0) return;
+        dim3 g((unsigned)p, (unsigned)S);
+        tile_kernel<OP_TRTRI_FIN><<<g, T_THREADS, T_SMEM_BYTES, st>>>(n, p, W, ldw, L, ldl, dinv, 0);
+        count_launches(1);
+    };
+    if (left) {
+        for (int p = 1; p < T; ++p) {
             dim3 g((unsigned)p, (unsigned)S);
-            if (left) {
-                tile_kernel<OP_TRTRI_ACC><<<g, T_THREADS, T_SMEM_BYTES, st>>>(n, p, W, ldw, L, ldl, dinv, 0);
+            tile_kernel<OP_TRTRI_ACC><<<g, T_THREADS, T_SMEM_BYTES, st>>>(n, p, W, ldw, L, ldl, dinv, 0);
+            count_launches(1);
+            fin(p);
+        }
+    } else {
+        // double steps (p, p+1): finish row p, bring row p+1 up to date with a rank-NB update
+        // from row p alone, finish it, then update every row below with ONE rank-2NB pass
+        for (int p = 0; p < T; p += 2) {
+            fin(p);
+            if (p + 1 >= T) break;
+            {
+                dim3 g((unsigned)(p + 1), (unsigned)S);      // tiles (p+1, j), j <= p
+                tile_kernel<OP_TRTRI_RIGHT><<<g, T_THREADS, T_SMEM_BYTES, st>>>(n, p, W, ldw, L, ldl, dinv, 0);
                 count_launches(1);
             }
-            tile_kernel<OP_TRTRI_FIN><<<g, T_THREADS, T_SMEM_BYTES, st>>>(n, p, W, ldw, L, ldl, dinv, 0);
-            count_launches(1);
-        }
-        if (!left && p + 1 < T) {
-            dim3 g((unsigned)((int64_t)(T - p - 1) * (p + 1)), (unsigned)S);
-            tile_kernel<OP_TRTRI_RIGHT><<<g, T_THREADS, T_SMEM_BYTES, st>>>(n, p, W, ldw, L, ldl, dinv, 0);
-            count_launches(1);
+            fin(p + 1);
+            if (p + 2 < T) {
+                dim3 g((unsigned)((int64_t)(T - p - 2) * (p + 2)), (unsigned)S);
+                tile_kernel<OP_TRTRI_RIGHT2><<<g, T_THREADS, T_SMEM_BYTES, st>>>(n, p, W, ldw, L, ldl, dinv, 0);
+                count_launches(1);
+            }
         }
     }
     GPX_LAUNCH_CHECK();
