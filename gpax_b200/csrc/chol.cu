@@ -10,6 +10,7 @@
 // p only; each tile is read and written once -- used when S gives enough
 // parallelism) and RIGHT-looking (rank-NB update of the whole trailing matrix --
 // used for few large matrices, e.g. n = 16384, S = 1).
+#include <cstdlib>
 #include <mutex>
 #include "mma_tile.cuh"
 
@@ -407,6 +408,21 @@ static int potrf_right_lookahead(int64_t S, int64_t n, int T, double *A, int64_t
     return 0;
 }
 
+// schedule: left-looking when the batch alone fills the machine; GPX_CHOL_SCHEDULE=left|right
+// overrides the choice (measurements only)
+static bool choose_left(int64_t S, int T) {
+    static int forced = -1;
+    if (forced < 0) {
+        const char *e = getenv("GPX_CHOL_SCHEDULE");
+        forced = !e ? 0 : (e[0] == 'l' ? 1 : (e[0] == 'r' ? 2 : 0));
+    }
+    if (forced == 1) return true;
+    if (forced == 2) return false;
+    // measured on B200 at n = 2048: right-looking (double steps + look-ahead) wins at S = 16 and 64
+    // (S*T/2 = 128, 512), left-looking at S = 296 and 1000 (2368, 8000)
+    return S * (int64_t)((T + 1) / 2) >= 1024;
+}
+
 }  // namespace gpx
 
 extern "C" size_t gpx_dinv_bytes(int64_t S, int64_t n) {
@@ -429,7 +445,7 @@ extern "C" int gpx_potrf_batched(int64_t S, int64_t n, double *A, int64_t lda, d
     if (info) cudaMemsetAsync(info, 0, sizeof(int32_t) * S, st);
     const int T = (int)((n + NB - 1) / NB);
     // schedule: left-looking when the batch alone fills the machine
-    const bool left = (S * (int64_t)((T + 1) / 2) >= 296);
+    const bool left = choose_left(S, T);
     if (!left && T >= 4) {
         rc = potrf_right_lookahead(S, n, T, A, lda, dinv, info, st);
         if (rc >= 0) return rc;     // < 0: side stream unavailable, fall through to the plain schedule
@@ -482,7 +498,7 @@ extern "C" int gpx_trtri_batched(int64_t S, int64_t n, const double *L, int64_t 
     // (deep-K sum per tile, p tiles per launch) when the batch fills the machine;
     // RIGHT-looking (rank-NB update of every row below p, (T-p-1)(p+1) tiles per launch)
     // for few large matrices, where a block row alone is less than one wave.
-    const bool left = (S * (int64_t)((T + 1) / 2) >= 296);
+    const bool left = choose_left(S, T);
     auto fin = [&](int p) {          // W(p, j) <- -Dinv(p) W(p, j), j < p
         if (p == 0) return;
         dim3 g((unsigned)p, (unsigned)S);

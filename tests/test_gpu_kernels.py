@@ -593,3 +593,34 @@ def test_hot_path_is_cuda_graph_capturable(cuda):
     assert torch.equal(val_g, val_e)
     for a, e in zip(out_g, out_e):
         assert torch.equal(a, e)
+
+
+@pytest.mark.parametrize("schedule", ["left", "right"])
+def test_cholesky_schedules_agree_with_lapack(cuda, schedule):
+    """gpx_potrf_batched / gpx_trtri_batched pick a left- or right-looking schedule from the batch
+    size; GPX_CHOL_SCHEDULE forces one (read once per process, hence the subprocess).  Both must
+    reproduce LAPACK's factor and its inverse on a batch with a ragged last block (n = 777, T = 7)."""
+    import os, subprocess, sys, textwrap
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    code = textwrap.dedent("""
+        import sys; sys.path.insert(0, %r)
+        import numpy as np, torch, scipy.linalg as sl
+        from gpax_b200 import engine as E, synthetic as syn, _cabi
+        from oracle import gp_oracle as O
+        rng = np.random.default_rng(5); n, d, S = 777, 2, 3
+        x = rng.uniform(-1, 1, (n, d)); hp = syn.draw_hp(rng, S, 1)
+        dev = torch.device("cuda:0"); hpd = E.HyperParams("matern52", d, hp, dev); xd = E._dev(x, dev)
+        L = E.gram(hpd, xd, xd, add_diag=True, region=_cabi.LOWER)
+        dinv, info = E.potrf(L, n); W = E.trtri(L, n, dinv); torch.cuda.synchronize()
+        assert int(info.abs().max()) == 0
+        K = O.gram_batched("matern52", x, x, hp, apply_noise=True)
+        for s in range(S):
+            Lr = sl.cholesky(K[s], lower=True)
+            Lg = np.tril(L[s, :, :n].cpu().numpy()); Wg = np.tril(W[s, :, :n].cpu().numpy())
+            assert np.max(np.abs(Lg - Lr)) / np.max(np.abs(Lr)) < 1e-11
+            assert np.max(np.abs(Wg @ Lr - np.eye(n))) < 1e-8
+        print("ok")
+    """ % root)
+    env = dict(os.environ, GPX_CHOL_SCHEDULE=schedule)
+    out = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0 and "ok" in out.stdout, out.stderr[-2000:]
