@@ -44,10 +44,16 @@ constexpr int W_BK = 16;                       // 128-byte rows = one swizzle sp
 constexpr int W_GEN_AHEAD = 2;                 // K* slices are generated this many slices ahead
 constexpr int W_NK = 5;                        // K* ring slots (>= GEN_AHEAD + 2: no "empty" barrier needed)
 constexpr int W_MF = 8, W_NF = 4;              // per-warp fragment grid: 64 rows x 32 candidates
-constexpr int W_NX = 4;                        // staged-training-row ring slots (>= GEN_AHEAD + 2, like W_NK)
+// Staged-training-row ring.  Rows of slice g + 1 arrive on their own mbarrier (4 slots, one poll
+// per slice) when the rows are wide (DMAX = 8: 6 slots would not fit the 227 KB); for DMAX <= 4 the
+// rows of slice g + GEN_AHEAD + 1 ride on the fullW barrier of slice g's W slab, which every
+// thread waits on anyway one iteration before it needs them: no poll of their own, 6 slots
+// (>= 2 GEN_AHEAD + 2, same argument as for W_NK with the longer distance).
+__host__ __device__ constexpr bool xrows_ride(int dmax) { return dmax <= 4; }
+__host__ __device__ constexpr int nx_of(int dmax) { return xrows_ride(dmax) ? 6 : 4; }
 // shared memory of predict_ws_kernel<KIND, WN, DMAX>: WCfg<WN>::SMEM_BYTES + the row ring + its barriers
 __host__ __device__ constexpr size_t xring_bytes(int dmax) {
-    return (size_t)W_NX * W_BK * (dmax + 2) * sizeof(double) + W_NX * sizeof(uint64_t);
+    return (size_t)nx_of(dmax) * W_BK * (dmax + 2) * sizeof(double) + nx_of(dmax) * sizeof(uint64_t);
 }
 
 template <int WN>
@@ -287,6 +293,8 @@ predict_ws_kernel(const __grid_constant__ CUtensorMap tmW, gpx_kernel_params kp,
     double *smean = wpart + WM * C::MT;                   // [GEN][W_THREADS]
     double *s_len = smean + W_THREADS * C::GEN;           // [MAX_D]
     double *s_per = s_len + GPX_MAX_D;                    // [MAX_D]
+    constexpr int W_NX = nx_of(DMAX);
+    constexpr bool RIDE = xrows_ride(DMAX);
     double *sXr = s_per + GPX_MAX_D;                      // [W_NX][W_BK][XSP] staged training rows (16-byte aligned)
     uint64_t *bars = reinterpret_cast<uint64_t *>(sXr + W_NX * W_BK * XSP);
 
@@ -386,6 +394,9 @@ predict_ws_kernel(const __grid_constant__ CUtensorMap tmW, gpx_kernel_params kp,
     const uint32_t xrow_u = sXr_u + (uint32_t)(gk * XSP) * 8u;
     int gi = 0, g_rb = 0, g_c = 0, g_nsl = nsl_of(0);     // next slice to generate
     uint32_t gslot = 0;                                   // its K* ring slot
+    uint32_t xslot = 0, xph = 0;                          // its staged-row ring slot / phase
+    // RIDE: k-slice position of slice gi + D + 1 (the first row block has > D + 1 slices: n > 128)
+    int xa_c = D + 1, xa_rb = 0, xa_nsl = nsl_of(0);
     double macc[GEN];
 #pragma unroll
     for (int i = 0; i < GEN; ++i) macc[i] = 0.0;
@@ -393,10 +404,9 @@ predict_ws_kernel(const __grid_constant__ CUtensorMap tmW, gpx_kernel_params kp,
     // gen_begin: distances of this thread's GEN entries of slice gi
     auto gen_begin = [&](Gen &g, double &al) {
         double2 xr[XSP / 2];
-        mbar_wait(bar_fullX + 8 * (gi & (W_NX - 1)), (gi / W_NX) & 1);
+        if constexpr (!RIDE) mbar_wait(bar_fullX + 8 * xslot, xph);
 #pragma unroll
-        for (int q = 0; q < XSP / 2; ++q)
-            xr[q] = lds128(xrow_u + (uint32_t)(gi & (W_NX - 1)) * X_BYTES + q * 16);
+        for (int q = 0; q < XSP / 2; ++q) xr[q] = lds128(xrow_u + xslot * X_BYTES + q * 16);
         auto xr_at = [&](int q) { return (q & 1) ? xr[q >> 1].y : xr[q >> 1].x; };
 #pragma unroll
         for (int i = 0; i < GEN; ++i) {
@@ -436,29 +446,44 @@ predict_ws_kernel(const __grid_constant__ CUtensorMap tmW, gpx_kernel_params kp,
         }
         al = xr_at(DMAX + 1);
     };
-    // x_issue (the elected TMA thread): rows of slice g (k offset c16 * 16) -> ring slot g % W_NX.
-    // The slot last held slice g - W_NX, whose readers all passed before the fullK barrier that
-    // the issuing thread has already waited on (same argument as for the K* ring below).
-    auto x_issue = [&](int g, int c16) {
-        const uint32_t xb = bar_fullX + 8 * (g & (W_NX - 1));
-        mbar_arrive_expect_tx(xb, X_BYTES);
-        bulk_load(sXr_u + (uint32_t)(g & (W_NX - 1)) * X_BYTES, xs_s + (size_t)c16 * W_BK * XSP, X_BYTES, xb);
+    // x_issue (the elected TMA thread): 16 staged rows at k offset c16 * 16 -> ring slot `slot`,
+    // completing on mbarrier `bar` (whose expect_tx the caller has raised by X_BYTES).  The slot last
+    // held a slice whose readers all passed before a fullK barrier the issuing thread has already
+    // waited on (same argument as for the K* ring below).
+    auto x_copy = [&](uint32_t slot, int c16, uint32_t bar) {
+        bulk_load(sXr_u + slot * X_BYTES, xs_s + (size_t)c16 * W_BK * XSP, X_BYTES, bar);
     };
     // tma_issue (one elected thread): as soon as the stage of slice gi is released,
     // stream the W slab of that slice into it -- two slices ahead of its use
     auto tma_issue = [&]() {
-        if (gi + 1 < T) x_issue(gi + 1, (g_c + 1 < g_nsl) ? g_c + 1 : 0);
+        if constexpr (!RIDE) {
+            if (gi + 1 < T) {      // rows of the next slice to generate, on their own barrier
+                const uint32_t sl = (xslot + 1 == W_NX) ? 0 : xslot + 1;
+                mbar_arrive_expect_tx(bar_fullX + 8 * sl, X_BYTES);
+                x_copy(sl, (g_c + 1 < g_nsl) ? g_c + 1 : 0, bar_fullX + 8 * sl);
+            }
+        }
         const uint32_t gst = gi % C::NST, gph = (gi / C::NST) & 1;
         mbar_wait(bar_emptyW + 8 * gst, gph ^ 1);
+        const bool ride = RIDE && (gi + D + 1 < T);   // rows of slice gi + D + 1 ride on this stage's barrier
+        uint32_t rslot = xslot + D + 1;
+        if (rslot >= W_NX) rslot -= W_NX;
         if (DBG & 4) {
-            mbar_arrive(bar_fullW + 8 * gst);
+            if (ride) {
+                mbar_arrive_expect_tx(bar_fullW + 8 * gst, X_BYTES);
+                x_copy(rslot, xa_c, bar_fullW + 8 * gst);
+            } else {
+                mbar_arrive(bar_fullW + 8 * gst);
+            }
             return;
         }
-        mbar_arrive_expect_tx(bar_fullW + 8 * gst, (uint32_t)(C::W_STAGE * sizeof(double)));
+        mbar_arrive_expect_tx(bar_fullW + 8 * gst,
+                              (uint32_t)(C::W_STAGE * sizeof(double)) + (ride ? X_BYTES : 0u));
 #pragma unroll
         for (int b = 0; b < C::NBOX; ++b)
             tma_load_3d(sW_u + (gst * C::W_STAGE + b * C::BOX_ROWS * W_BK) * 8, &tmW,
                         bar_fullW + 8 * gst, g_c * W_BK, g_rb * C::R + b * C::BOX_ROWS, s);
+        if (ride) x_copy(rslot, xa_c, bar_fullW + 8 * gst);
     };
     // gen_end: publish the entries into the K* slot of slice gi
     auto gen_end = [&](Gen &g, double al) {
@@ -472,15 +497,29 @@ predict_ws_kernel(const __grid_constant__ CUtensorMap tmW, gpx_kernel_params kp,
         __syncwarp();
         if (lane == 0) mbar_arrive(bar_fullK + 8 * gslot);
         if (++gslot == W_NK) gslot = 0;
+        if (++xslot == W_NX) { xslot = 0; xph ^= 1; }
         ++gi;
         if (++g_c == g_nsl) {
             g_c = 0;
             ++g_rb;
             g_nsl = g_rb < NRB ? nsl_of(g_rb) : 1;
         }
+        if (RIDE) {          // position of slice gi + D + 1 (uniform in every thread: any lane may be elected)
+            if (++xa_c == xa_nsl) {
+                xa_c = 0;
+                ++xa_rb;
+                xa_nsl = xa_rb < NRB ? nsl_of(xa_rb) : 1;
+            }
+        }
     };
     // prologue: the first D slices
-    if (warp == 0 && elect_one()) x_issue(0, 0);
+    if (warp == 0 && elect_one()) {
+        // rows of the first slices on fullX[0] (RIDE: slices 0..D, nothing precedes them; else slice 0)
+        const int n0 = RIDE ? (T < D + 1 ? T : D + 1) : 1;
+        mbar_arrive_expect_tx(bar_fullX, (uint32_t)n0 * X_BYTES);
+        for (int q = 0; q < n0; ++q) x_copy((uint32_t)q, q, bar_fullX);
+    }
+    if constexpr (RIDE) mbar_wait(bar_fullX, 0);
     for (int q = 0; q < D && gi < T; ++q) {
         Gen g;
         double al;
