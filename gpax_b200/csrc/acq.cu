@@ -80,6 +80,32 @@ __device__ __forceinline__ double acq_value(int acq, double mu, double sd, doubl
     return mu;
 }
 
+// Mixture moments over the posterior samples, accumulated in the fixed order s = 0..S-1
+// around the shift c = mu of sample 0 (the RNG-free limit of np.mean / np.std over the pooled
+// draws, gpax/gp.py:76-90, which is a two-pass and therefore cancellation-free computation):
+//   mbar = c + mean_s(mu_s - c);   vbar = mean_s(var_s) + [mean_s (mu_s - c)^2 - (mean_s(mu_s - c))^2]
+// The bracket is the population variance of the means; it cancels only on the scale of their own
+// spread, never on the scale of |mu|, and is clipped at 0 (a variance; NaN is preserved).
+// mean_s(var_s) is NOT clipped: a negative per-sample variance gives NaN downstream exactly as the
+// reference's sqrt(diag cov) does (gpax/gp.py:338).
+struct Mix {
+    double c, a, bv, bd;
+    __device__ __forceinline__ void begin(double c0) { c = c0; a = 0.0; bv = 0.0; bd = 0.0; }
+    __device__ __forceinline__ void add(double m1, double v1) {
+        const double dm = m1 - c;
+        a = a + dm;
+        bv = bv + v1;
+        bd = bd + dm * dm;
+    }
+    __device__ __forceinline__ void finish(int64_t S, double &mbar, double &vbar) const {
+        const double ab = a / (double)S;
+        double spread = bd / (double)S - ab * ab;
+        spread = spread < 0.0 ? 0.0 : spread;
+        mbar = c + ab;
+        vbar = bv / (double)S + spread;
+    }
+};
+
 __global__ void __launch_bounds__(A_THREADS)
 acq_reduce_kernel(int64_t S, int64_t M, const double *__restrict__ mu,
                   const double *__restrict__ var, int acq, double coef, double y_max,
@@ -97,7 +123,8 @@ acq_reduce_kernel(int64_t S, int64_t M, const double *__restrict__ mu,
             mbar = mu[j];
             vbar = var[j];
         } else {
-            double a = 0.0, b = 0.0;
+            Mix mx;
+            mx.begin(mu[j]);
             int64_t s = 0;
             for (; s + 8 <= S; s += 8) {
                 double m_[8], v_[8];
@@ -107,18 +134,10 @@ acq_reduce_kernel(int64_t S, int64_t M, const double *__restrict__ mu,
                     v_[q] = var[(s + q) * M + j];
                 }
 #pragma unroll
-                for (int q = 0; q < 8; ++q) {
-                    a = a + m_[q];
-                    b = b + (v_[q] + m_[q] * m_[q]);
-                }
+                for (int q = 0; q < 8; ++q) mx.add(m_[q], v_[q]);
             }
-            for (; s < S; ++s) {
-                double m1 = mu[s * M + j], v1 = var[s * M + j];
-                a = a + m1;
-                b = b + (v1 + m1 * m1);
-            }
-            mbar = a / (double)S;
-            vbar = b / (double)S - mbar * mbar;
+            for (; s < S; ++s) mx.add(mu[s * M + j], var[s * M + j]);
+            mx.finish(S, mbar, vbar);
         }
         const double mu_u = mbar * mu_scale + mu_shift;
         const double sd_u = sqrt(vbar) * sd_scale;
@@ -178,10 +197,11 @@ acq_reduce_narrow_kernel(int64_t S, int64_t M, const double *__restrict__ mu,
             s_var[buf][warp * RPW + q][lane] = rv[q];
         }
     };
-    double a = 0.0, b = 0.0;
+    Mix mx;
     fetch(0);
     stash(0);
     __syncthreads();
+    mx.begin(s_mu[0][0][lane]);
     int buf = 0;
     for (int64_t s0 = 0; s0 < S; s0 += A_ROWS) {
         const bool more = s0 + A_ROWS < S;
@@ -190,17 +210,9 @@ acq_reduce_narrow_kernel(int64_t S, int64_t M, const double *__restrict__ mu,
             const int rows = (int)((S - s0 < A_ROWS) ? (S - s0) : A_ROWS);
             if (rows == A_ROWS) {
 #pragma unroll 8
-                for (int r = 0; r < A_ROWS; ++r) {
-                    const double m1 = s_mu[buf][r][lane], v1 = s_var[buf][r][lane];
-                    a = a + m1;
-                    b = b + (v1 + m1 * m1);
-                }
+                for (int r = 0; r < A_ROWS; ++r) mx.add(s_mu[buf][r][lane], s_var[buf][r][lane]);
             } else {
-                for (int r = 0; r < rows; ++r) {
-                    const double m1 = s_mu[buf][r][lane], v1 = s_var[buf][r][lane];
-                    a = a + m1;
-                    b = b + (v1 + m1 * m1);
-                }
+                for (int r = 0; r < rows; ++r) mx.add(s_mu[buf][r][lane], s_var[buf][r][lane]);
             }
         }
         if (more) stash(buf ^ 1);
@@ -217,8 +229,7 @@ acq_reduce_narrow_kernel(int64_t S, int64_t M, const double *__restrict__ mu,
             mbar = mu[j];                        // S == 1: analytic pass-through (the `fast` path),
             vbar = var[j];                       // not (var + mu*mu) - mu*mu
         } else {
-            mbar = a / (double)S;
-            vbar = b / (double)S - mbar * mbar;
+            mx.finish(S, mbar, vbar);
         }
         const double mu_u = mbar * mu_scale + mu_shift;
         const double sd_u = sqrt(vbar) * sd_scale;

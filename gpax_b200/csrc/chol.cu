@@ -275,12 +275,8 @@ trtri_diag_copy_kernel(int64_t n, const double *__restrict__ dinv, double *__res
 }
 
 static int set_attrs_once() {
-    static int done = 0;
-    if (done) return 0;
-    cudaError_t e;
-#define GPX_SET(K, BYTES)                                                                  \
-    e = cudaFuncSetAttribute(K, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(BYTES)); \
-    if (e != cudaSuccess) return (int)e;
+#define GPX_SET(K, BYTES) \
+    if (int e = ensure_smem(K, BYTES)) return e;
     GPX_SET(diag_kernel, DIAG_SMEM);
     GPX_SET(tile_kernel<OP_SYRK_LEFT>, T_SMEM_BYTES);
     GPX_SET(tile_kernel<OP_SYRK_RIGHT>, T_SMEM_BYTES);
@@ -293,26 +289,44 @@ static int set_attrs_once() {
     GPX_SET(tile_kernel<OP_TRTRI_RIGHT>, T_SMEM_BYTES);
     GPX_SET(tile_kernel<OP_TRTRI_RIGHT2>, T_SMEM_BYTES);
 #undef GPX_SET
-    done = 1;
     return 0;
 }
 
-// High-priority side stream of the calling thread's current device (created once per device).
-static cudaStream_t side_stream() {
+// Fork / join resources of the look-ahead schedule: one high-priority side stream per device
+// (shared by all host threads; streams are thread-safe) and one pair of timing-less events per
+// (host thread, device).  Created on first use and kept for the life of the process, so steady-
+// state calls create nothing; a thread's consecutive calls may re-record its events (a pending
+// cudaStreamWaitEvent keeps the state it captured).
+struct ForkJoin {
+    cudaStream_t side = nullptr;
+    cudaEvent_t ev_panel = nullptr, ev_side = nullptr;
+};
+static int fork_join(ForkJoin &out) {
     static cudaStream_t streams[64] = {};
     static std::mutex mu;
+    thread_local cudaEvent_t events[64][2] = {};
     int dev = 0;
-    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
-    std::lock_guard<std::mutex> lock(mu);
-    if (!streams[dev]) {
-        int lo = 0, hi = 0;
-        cudaDeviceGetStreamPriorityRange(&lo, &hi);      // hi = numerically lowest = greatest priority
-        if (cudaStreamCreateWithPriority(&streams[dev], cudaStreamNonBlocking, hi) != cudaSuccess) {
-            streams[dev] = nullptr;
-            cudaGetLastError();
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return (int)e;
+    if (dev < 0 || dev >= 64) return (int)cudaErrorInvalidDevice;
+    {
+        std::lock_guard<std::mutex> lock(mu);
+        if (!streams[dev]) {
+            int lo = 0, hi = 0;
+            cudaDeviceGetStreamPriorityRange(&lo, &hi);      // hi = numerically lowest = greatest priority
+            e = cudaStreamCreateWithPriority(&streams[dev], cudaStreamNonBlocking, hi);
+            if (e != cudaSuccess) { streams[dev] = nullptr; return (int)e; }
         }
     }
-    return streams[dev];
+    for (int i = 0; i < 2; ++i)
+        if (!events[dev][i]) {
+            e = cudaEventCreateWithFlags(&events[dev][i], cudaEventDisableTiming);
+            if (e != cudaSuccess) { events[dev][i] = nullptr; return (int)e; }
+        }
+    out.side = streams[dev];
+    out.ev_panel = events[dev][0];
+    out.ev_side = events[dev][1];
+    return 0;
 }
 
 // Right-looking Cholesky with one block column of look-ahead, for few large matrices (C4:
@@ -321,18 +335,19 @@ static cudaStream_t side_stream() {
 // latency-bound) and its TRSM then run on a high-priority side stream while the main stream
 // applies the rank-128 update of step p to the rest of the trailing matrix (columns >= p + 2).
 // Fork / join by events only, so the call stays asynchronous and graph-capturable.
-// Returns 0 / cudaError_t, or -1 when no side stream could be created (nothing enqueued).
+// Returns 0 / cudaError_t (also when the side stream or the events cannot be created: there is no
+// silent fall-back to the slower schedule).
 static int potrf_right_lookahead(int64_t S, int64_t n, int T, double *A, int64_t lda, double *dinv,
                                  int32_t *info, cudaStream_t st) {
-    cudaStream_t ss = side_stream();
-    if (!ss) return -1;
-    cudaEvent_t ev_panel = nullptr, ev_side = nullptr;
-    if (cudaEventCreateWithFlags(&ev_panel, cudaEventDisableTiming) != cudaSuccess ||
-        cudaEventCreateWithFlags(&ev_side, cudaEventDisableTiming) != cudaSuccess) {
-        if (ev_panel) cudaEventDestroy(ev_panel);
+    ForkJoin fj;
+    if (int rc = fork_join(fj)) {
+        set_error("gpx_potrf_batched: look-ahead stream / events unavailable: CUDA error %d (%s)", rc,
+                  cudaGetErrorString((cudaError_t)rc));
         cudaGetLastError();
-        return -1;
+        return rc;
     }
+    cudaStream_t ss = fj.side;
+    cudaEvent_t ev_panel = fj.ev_panel, ev_side = fj.ev_side;
     auto diag_trsm = [&](int p, cudaStream_t q) {
         diag_kernel<<<(unsigned)S, 256, DIAG_SMEM, q>>>(n, p, A, lda, dinv, info);
         count_launches(1);
@@ -398,8 +413,6 @@ static int potrf_right_lookahead(int64_t S, int64_t n, int T, double *A, int64_t
         cudaStreamWaitEvent(st, ev_side, 0);     // join: step p + 1 needs column p + 1 solved
     }
     }
-    cudaEventDestroy(ev_panel);                  // released once the pending work has used them
-    cudaEventDestroy(ev_side);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) {
         set_error("gpx_potrf_batched: CUDA error %d (%s)", (int)e, cudaGetErrorString(e));
@@ -440,16 +453,13 @@ extern "C" int gpx_potrf_batched(int64_t S, int64_t n, double *A, int64_t lda, d
     GPX_ARG_CHECK(dinv != nullptr || S * n == 0, 5);
     if (S == 0 || n == 0) return 0;
     int rc = set_attrs_once();
-    if (rc) { set_error("cudaFuncSetAttribute failed: %d", rc); return rc; }
+    if (rc) return rc;
     cudaStream_t st = (cudaStream_t)stream;
     if (info) cudaMemsetAsync(info, 0, sizeof(int32_t) * S, st);
     const int T = (int)((n + NB - 1) / NB);
     // schedule: left-looking when the batch alone fills the machine
     const bool left = choose_left(S, T);
-    if (!left && T >= 4) {
-        rc = potrf_right_lookahead(S, n, T, A, lda, dinv, info, st);
-        if (rc >= 0) return rc;     // < 0: side stream unavailable, fall through to the plain schedule
-    }
+    if (!left && T >= 4) return potrf_right_lookahead(S, n, T, A, lda, dinv, info, st);
     for (int p = 0; p < T; ++p) {
         if (left && p > 0) {
             dim3 g((unsigned)(T - p), (unsigned)S);
@@ -486,7 +496,7 @@ extern "C" int gpx_trtri_batched(int64_t S, int64_t n, const double *L, int64_t 
     GPX_ARG_CHECK(ldw >= n && (ldw % 2 == 0), 7);
     if (S == 0 || n == 0) return 0;
     int rc = set_attrs_once();
-    if (rc) { set_error("cudaFuncSetAttribute failed: %d", rc); return rc; }
+    if (rc) return rc;
     cudaStream_t st = (cudaStream_t)stream;
     const int T = (int)((n + NB - 1) / NB);
     {

@@ -16,6 +16,10 @@ namespace gpx {
 // ---- error plumbing -------------------------------------------------------
 void set_error(const char *fmt, ...);
 void count_launches(int n);   // feeds gpx_launch_count()
+// per-(device, kernel) one-time raise of the dynamic shared memory limit (thread-safe)
+int ensure_dyn_smem(const void *func, size_t bytes);
+template <class K>
+inline int ensure_smem(K kernel, size_t bytes) { return ensure_dyn_smem((const void *)kernel, bytes); }
 #define GPX_ARG_CHECK(cond, argno)                                             \
     do {                                                                       \
         if (!(cond)) {                                                         \
@@ -102,7 +106,7 @@ __device__ __forceinline__ void exp_vec(double (&x)[N]) {
     int ni[N];
     double nf[N], p[N];
 #pragma unroll
-    for (int i = 0; i < N; ++i) x[i] = fmax(x[i], -1000.0);
+    for (int i = 0; i < N; ++i) x[i] = x[i] < -1000.0 ? -1000.0 : x[i];   // NaN passes through (fmax would swallow it)
 #pragma unroll
     for (int i = 0; i < N; ++i) {
         double t = fma(x[i], L2E, SHIFT);

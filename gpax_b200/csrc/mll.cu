@@ -307,13 +307,7 @@ extern "C" int gpx_mll(int64_t S, int64_t n, const double *L, int64_t ldl, const
     }
     size_t smem = (size_t)(T * MNB + 2 * MNB + MTHREADS) * sizeof(double);
     GPX_ARG_CHECK(smem <= 227 * 1024, 2);   // n <= ~28k for the single-CTA solve
-    static size_t configured = 0;
-    if (smem > configured) {
-        cudaError_t e = cudaFuncSetAttribute(mll_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                             (int)smem);
-        if (e != cudaSuccess) { set_error("gpx_mll: smem attribute failed (%d)", (int)e); return (int)e; }
-        configured = smem;
-    }
+    if (int e = ensure_smem(mll_kernel, smem)) return e;
     mll_kernel<<<(unsigned)S, MTHREADS, smem, st>>>(n, L, ldl, dinv, resid,
                                                                       resid_stride, alpha, mll);
     count_launches(1);

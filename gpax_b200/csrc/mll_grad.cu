@@ -180,14 +180,7 @@ extern "C" int gpx_mll_grad(const gpx_kernel_params *kp, int64_t S, int64_t n, c
     GPX_ARG_CHECK(alpha != nullptr || S * n == 0, 7);
     GPX_ARG_CHECK(ws != nullptr || S * n == 0, 12);
     if (S == 0 || n == 0) return 0;
-    static bool configured = false;
-    if (!configured) {
-        cudaError_t e = cudaFuncSetAttribute(mll_grad_tile_kernel,
-                                             cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                             (int)T_SMEM_BYTES);
-        if (e != cudaSuccess) { set_error("gpx_mll_grad: smem attribute failed (%d)", (int)e); return (int)e; }
-        configured = true;
-    }
+    if (int e = ensure_smem(mll_grad_tile_kernel, T_SMEM_BYTES)) return e;
     cudaStream_t st = (cudaStream_t)stream;
     const int64_t T = (n + TM - 1) / TM;
     const int64_t ntiles = T * (T + 1) / 2;

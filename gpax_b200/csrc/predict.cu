@@ -705,14 +705,7 @@ static int launch_predict_ws(const gpx_kernel_params *kp, int64_t S, int64_t n, 
                              const double *m_new, double m_const, const double *diag_add,
                              double *mu, double *var, int64_t ldo, int64_t ldmn, cudaStream_t st) {
     using C = WCfg<WN>;
-    static bool configured = false;
-    if (!configured) {
-        cudaError_t e = cudaFuncSetAttribute(predict_ws_kernel<KIND, WN, DMAX>,
-                                             cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                             (int)(C::SMEM_BYTES + xring_bytes(DMAX)));
-        if (e != cudaSuccess) { set_error("gpx_predict: smem attribute failed (%d)", (int)e); return (int)e; }
-        configured = true;
-    }
+    if (int e = ensure_smem(predict_ws_kernel<KIND, WN, DMAX>, C::SMEM_BYTES + xring_bytes(DMAX))) return e;
     CUtensorMap tm;
     int rc = make_w_tensormap(&tm, W, S, n, ldw, C::BOX_ROWS);
     if (rc) return rc;
@@ -724,8 +717,7 @@ static int launch_predict_ws(const gpx_kernel_params *kp, int64_t S, int64_t n, 
         if (dbg < 0) { const char *e = getenv("GPX_PREDICT_DEBUG"); dbg = e ? atoi(e) : 0; }
 #define GPX_DBG_CASE(D)                                                                            \
         case D: {                                                                                  \
-            static bool cfg = false;                                                               \
-            if (!cfg) { cudaFuncSetAttribute(predict_ws_kernel<GPX_MATERN52, 1, 2, D>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(C::SMEM_BYTES + xring_bytes(2))); cfg = true; } \
+            if (int e = ensure_smem(predict_ws_kernel<GPX_MATERN52, 1, 2, D>, C::SMEM_BYTES + xring_bytes(2))) return e; \
             predict_ws_kernel<GPX_MATERN52, 1, 2, D><<<grid, W_THREADS, C::SMEM_BYTES + xring_bytes(2), st>>>(      \
                 tm, *kp, (int)n, n_pad, (int)M, xs, xnew, m_new, m_const, diag_add, mu, var, ldo, ldmn);      \
             return 0; }

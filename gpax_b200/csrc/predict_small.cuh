@@ -297,13 +297,7 @@ static int launch_predict(const gpx_kernel_params *kp, int64_t S, int64_t n, int
                           const double *diag_add, double *mu, double *var, int64_t ldo, int64_t ldmn, cudaStream_t st) {
     using C = PCfg<WM, WN, BK>;
     const size_t smem = C::SMEM_DOUBLES * sizeof(double);
-    static bool configured = false;
-    if (!configured) {
-        cudaError_t e = cudaFuncSetAttribute(predict_kernel<KIND, WM, WN, BK>,
-                                             cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        if (e != cudaSuccess) { set_error("gpx_predict: smem attribute failed (%d)", (int)e); return (int)e; }
-        configured = true;
-    }
+    if (int e = ensure_smem(predict_kernel<KIND, WM, WN, BK>, smem)) return e;
     dim3 grid((unsigned)((M + C::MT - 1) / C::MT), (unsigned)S);
     predict_kernel<KIND, WM, WN, BK><<<grid, P_THREADS, smem, st>>>(
         *kp, (int)n, (int)M, x, xnew, W, ldw, alpha, m_new, m_const, diag_add, mu, var, ldo, ldmn);

@@ -259,14 +259,7 @@ static int launch_predict_tiny_d(const gpx_kernel_params *kp, int64_t S, int64_t
                                const double *alpha, const double *m_new, double m_const,
                                const double *diag_add, double *mu, double *var, int64_t ldo,
                                int64_t ldmn, cudaStream_t st) {
-    static bool configured = false;
-    if (!configured) {
-        cudaError_t e = cudaFuncSetAttribute(predict_tiny_kernel<KIND, DMAX>,
-                                             cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                             (int)T_SMEM_BYTES);
-        if (e != cudaSuccess) { set_error("gpx_predict: smem attribute failed (%d)", (int)e); return (int)e; }
-        configured = true;
-    }
+    if (int e = ensure_smem(predict_tiny_kernel<KIND, DMAX>, T_SMEM_BYTES)) return e;
     // candidates per CTA: long runs amortise the prologue (W_s + inputs, ~40 KB from L2), but
     // keep >= ~8 CTAs per SM in the grid so the tail stays short
     const int64_t tiles = (M + 255) / 256;

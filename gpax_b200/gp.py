@@ -76,8 +76,8 @@ class GPSample:
                                     np.std(self._y, axis=(0, 1)).squeeze())
             else:                               # its RNG-free limit
                 m = mu.mean(axis=0)
-                v = (sd**2 + mu**2).mean(axis=0) - m**2
-                self._cache["m"] = (m.squeeze(), np.sqrt(np.clip(v, 0.0, None)).squeeze())
+                v = (sd**2).mean(axis=0) + mu.var(axis=0)      # law of total variance, two-pass
+                self._cache["m"] = (m.squeeze(), np.sqrt(v).squeeze())
         return self._cache["m"]
 
     @property

@@ -14,9 +14,14 @@
  *    ld >= n (rows start 16-byte aligned).  Only the LOWER triangle (j <= i)
  *    of a symmetric / triangular matrix is referenced unless stated otherwise.
  *  - Functions only ENQUEUE work on `stream` (a cudaStream_t passed as void*);
- *    they never synchronise, never allocate, never touch the host copy of data.
- *    The caller owns every buffer including workspace (sizes from the *_bytes
- *    query functions).  All calls are CUDA-graph capturable and re-entrant.
+ *    they never synchronise, never allocate device memory, never touch the
+ *    host copy of data.  The caller owns every buffer including workspace
+ *    (sizes from the *_bytes query functions).  All calls are CUDA-graph
+ *    capturable, re-entrant and thread-safe; they act on the calling thread's
+ *    current device.  Process-lifetime resources are created on FIRST use only
+ *    (per device: the raised dynamic-shared-memory limits of the kernels and
+ *    one high-priority side stream for the look-ahead Cholesky; per host thread
+ *    and device: two timing-less events) -- steady-state calls create nothing.
  *  - Return value: 0 = ok; < 0 = argument #(-rc) invalid; > 0 = cudaError_t.
  *    Numerical failure (non-SPD pivot) is reported per matrix in `info[S]`
  *    like LAPACK (0 = ok, k = leading minor of order k not positive).
@@ -157,8 +162,10 @@ int gpx_predict(const gpx_kernel_params *kp, int64_t S, int64_t n, int64_t M,
 /* ---------------------------------------------------------------------------
  * gpx_acq_reduce: mixture moments over S (fixed order s = 0..S-1), reverse
  * output transform, analytic acquisition and per-block first-max argmax.
- *   mbar = mean_s mu;  vbar = mean_s(var + mu^2) - mbar^2   (RNG-free limit of
- *   GPSample.mu/sd, gpax/gp.py:76-90; S == 1 is the analytic `fast` path)
+ *   mbar = mean_s mu;  vbar = mean_s(var) + var_s(mu)   (RNG-free limit of the
+ *   two-pass np.mean / np.std of GPSample.mu/sd, gpax/gp.py:76-90, accumulated
+ *   around mu of sample 0 so it does not cancel when |mu| >> sd; S == 1 is the
+ *   analytic `fast` path)
  *   mu_u = mbar*mu_scale + mu_shift ; sd_u = sqrt(vbar)*sd_scale
  *     (NormalizeTransform reverse, gpax/transforms.py:312-317)
  *   acq: EI gpax/acquisition.py:291-298 | UCB :260-266 | UE | MEAN.

@@ -281,19 +281,38 @@ def median_hp(hp):
 
 def mixture_moments(mu, var):
     """RNG-free limit of ``GPSample.mu/sd`` pooled over (S,G) (gpax/gp.py:76-90):
-    ``mean_s mu_s`` and population variance ``mean_s(var_s + mu_s^2) - mubar^2``.
-    Sequential (s = 0..S-1) accumulation so the device kernel can match the
-    summation order bit-for-bit."""
+    the reference takes ``np.mean`` / ``np.std`` of the pooled draws (two-pass,
+    ddof=0).  Law of total variance: ``mean_s mu_s`` and ``mean_s var_s +
+    var_s(mu_s)``.  Written in NumPy's own two-pass form on purpose -- it is
+    independent of the device kernel's one-pass shifted accumulation."""
     S = mu.shape[0]
     if S == 1:          # analytic single-sample path (gpax/gp.py:78-79,86-87)
         return mu[0].copy(), var[0].copy()
+    return mu.mean(axis=0), var.mean(axis=0) + mu.var(axis=0)
+
+
+def mixture_moments_device_order(mu, var):
+    """Emulation of the DEVICE kernel's accumulation (``gpx_acq_reduce``: one pass
+    in the fixed order s = 0..S-1 around the shift ``c = mu[0]``, no FMA).  Not a
+    restatement of the reference -- it exists so the tests can assert that the
+    kernel is bit-stable (same bits for every sharding / tiling) and can compare
+    it with the independent two-pass :func:`mixture_moments` at a tolerance."""
+    S = mu.shape[0]
+    if S == 1:
+        return mu[0].copy(), var[0].copy()
+    c = mu[0].copy()
     a = np.zeros(mu.shape[1])
-    b = np.zeros(mu.shape[1])
+    bv = np.zeros(mu.shape[1])
+    bd = np.zeros(mu.shape[1])
     for s in range(S):
-        a = a + mu[s]
-        b = b + (var[s] + mu[s] * mu[s])
-    mbar = a / S
-    return mbar, b / S - mbar * mbar
+        dm = mu[s] - c
+        a = a + dm
+        bv = bv + var[s]
+        bd = bd + dm * dm
+    ab = a / S
+    spread = bd / S - ab * ab
+    spread = np.where(spread < 0.0, 0.0, spread)
+    return c + ab, bv / S + spread
 
 
 # --------------------------------------------------------------------------

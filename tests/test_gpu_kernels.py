@@ -162,9 +162,10 @@ def test_mll_grad_matches_oracle(cuda, kind, per):
 # cross the narrow kernel's 32-sample chunk boundary with a ragged tail
 @pytest.mark.parametrize("S,M", [(1, 1000), (17, 5003), (70, 999), (33, 64), (1, 303200), (5, 310001)])
 def test_acq_reduce_bit_exact(cuda, acq, beta, S, M):
-    """Mixture moments + EI/UCB/UE + argmax.  Moments and UCB are bit-exact vs the
-    NumPy oracle (same operation order, no FMA); EI within 1e-13 relative (erf/exp
-    ulps); argmax index identical."""
+    """Mixture moments + EI/UCB/UE + argmax.  Moments and UCB are bit-exact vs the NumPy
+    emulation of the kernel's accumulation order (no FMA) and within 1e-13 of the oracle's
+    independent two-pass moments; EI within 1e-13 relative (erf/exp ulps); argmax index
+    identical."""
     import torch
     from gpax_b200 import engine as E
     rng = np.random.default_rng(S * 1000 + M)
@@ -175,14 +176,14 @@ def test_acq_reduce_bit_exact(cuda, acq, beta, S, M):
                                              y_max, a, b, c, m_offset=10)
     bv, bi = E.argmax_finalize(pv, pi)
     torch.cuda.synchronize()
-    if S == 1:
-        mbar, vbar = mu[0], var[0]
-    else:
-        mbar, vbar = O.mixture_moments(mu, var)
+    mbar, vbar = O.mixture_moments_device_order(mu, var)
     mu_u = mbar * a + b
     sd_u = np.sqrt(vbar) * c
     np.testing.assert_array_equal(o_mu.cpu().numpy(), mu_u)
     np.testing.assert_array_equal(o_sd.cpu().numpy(), sd_u)
+    mb2, vb2 = O.mixture_moments(mu, var)            # independent two-pass form
+    assert np.max(np.abs(mbar - mb2)) < 1e-13 * max(1.0, np.max(np.abs(mb2)))
+    assert np.max(np.abs(vbar - vb2) / vb2) < 1e-13
     ref = O.acquisition(acq, mu_u, sd_u, beta, y_max)
     got = o_acq.cpu().numpy()
     if acq == 0:
@@ -192,6 +193,31 @@ def test_acq_reduce_bit_exact(cuda, acq, beta, S, M):
         np.testing.assert_array_equal(got, ref)
         assert int(bi.item()) - 10 == O.first_argmax(ref)
     assert bv.item() == got[int(bi.item()) - 10]
+
+
+@pytest.mark.parametrize("offset,sd", [(1e3, 1.0), (1e4, 0.1), (1e6, 1e-2), (-3e5, 1e-3)])
+@pytest.mark.parametrize("S,M", [(1000, 64), (37, 400000)])
+def test_acq_reduce_large_mean_offset(cuda, offset, sd, S, M):
+    """|mean| >> sd (un-normalised targets, output_transform=None): the mixture variance must
+    not cancel.  Reference semantics are np.mean / np.std over the pooled draws (two-pass,
+    gpax/gp.py:76-90); the kernel's shifted one-pass accumulation must agree with the
+    two-pass oracle to 1e-10 relative on the variance and never produce a negative one."""
+    import torch
+    from gpax_b200 import engine as E, _cabi
+    rng = np.random.default_rng(int(abs(offset)) + S)
+    mu = offset + sd * rng.normal(size=(S, M))
+    var = (sd * rng.uniform(0.5, 1.5, (S, M))) ** 2
+    o_mu, o_sd, o_acq, pv, pi = E.acq_reduce(E._dev(mu, cuda), E._dev(var, cuda), _cabi.ACQ_UCB, 10.0)
+    _, bi = E.argmax_finalize(pv, pi)
+    torch.cuda.synchronize()
+    mb, vb = O.mixture_moments(mu, var)
+    got_sd = o_sd.cpu().numpy()
+    assert np.all(np.isfinite(got_sd)) and np.all(got_sd > 0)
+    assert np.max(np.abs(got_sd**2 - vb) / vb) < 1e-10
+    assert np.max(np.abs(o_mu.cpu().numpy() - mb) / np.abs(mb)) < 1e-14
+    ref = O.ucb(mb, np.sqrt(vb), 10.0)
+    # the winner the kernel picked is a maximiser of the two-pass reference up to rounding
+    assert ref[int(bi.item())] >= ref.max() - 1e-9 * sd
 
 
 def test_argmax_ties_and_nan(cuda):

@@ -117,7 +117,7 @@ o, c = P.candidate_chunk(M, world, rank)
 assert off == o and mu_all.shape == (world * S_local, c)
 np.testing.assert_array_equal(mu_all.numpy(), full_mu[:, o:o + c])
 # fixed-order reduction of the chunk (stand-in for gpx_acq_reduce) + winner exchange
-mbar, vbar = O.mixture_moments(mu_all.numpy(), var_all.numpy())
+mbar, vbar = O.mixture_moments_device_order(mu_all.numpy(), var_all.numpy())
 acq = O.ucb(mbar, np.sqrt(vbar), 10.0)
 j = int(np.argmax(acq)) if c else 0
 bv = torch.tensor([acq[j] if c else -np.inf]); bi = torch.tensor([off + j if c else 2**62])
@@ -128,7 +128,7 @@ mus, vars_ = [], []
 for r in range(world):
     g = np.random.default_rng(100 + r)
     mus.append(g.normal(size=(S_local, M))); vars_.append(g.uniform(0.1, 1.0, (S_local, M)))
-mb, vb = O.mixture_moments(np.concatenate(mus), np.concatenate(vars_))
+mb, vb = O.mixture_moments_device_order(np.concatenate(mus), np.concatenate(vars_))
 ref = O.ucb(mb, np.sqrt(vb), 10.0)
 k = int(np.argmax(vals.numpy()))                       # first max over ranks == lowest index on ties
 assert int(idxs[k]) == int(np.argmax(ref)), (idxs, np.argmax(ref))

@@ -207,6 +207,19 @@ def test_mixture_moments_and_median():
     mbar, vbar = O.mixture_moments(mu, var)
     np.testing.assert_allclose(mbar, mu.mean(0), rtol=1e-14)
     np.testing.assert_allclose(vbar, (var + mu**2).mean(0) - mu.mean(0) ** 2, rtol=1e-12)
+    # the device-order emulation agrees with the two-pass form, also when |mu| >> sd
+    md, vd = O.mixture_moments_device_order(mu, var)
+    np.testing.assert_allclose(md, mbar, rtol=1e-14)
+    np.testing.assert_allclose(vd, vbar, rtol=1e-13)
+    big = 1e6 + 1e-2 * rng.normal(size=(1000, 5))
+    bv = np.full((1000, 5), 1e-4)
+    mb, vb = O.mixture_moments(big, bv)
+    md, vd = O.mixture_moments_device_order(big, bv)
+    np.testing.assert_allclose(vd, vb, rtol=1e-11)
+    np.testing.assert_allclose(vb, 1e-4 + big.var(0), rtol=1e-14)
+    # a pooled Monte-Carlo estimate (what the reference literally computes) converges to it
+    draws = big[:, None, :] + 1e-2 * rng.normal(size=(1000, 64, 5))
+    np.testing.assert_allclose(np.std(draws, axis=(0, 1)) ** 2, vb, rtol=0.05)
     m1, v1 = O.mixture_moments(mu[:1], var[:1])
     np.testing.assert_array_equal(m1, mu[0])
     hp = {"k_scale": rng.uniform(1, 2, 9), "k_length": rng.uniform(1, 2, (9, 2)), "k_period": None}
