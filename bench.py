@@ -7,9 +7,12 @@ One "step" = one full pass of the hot path over the synthetic workload:
   (mean, variance on all M candidates for all S samples) -> mixture + EI -> argmax.
 Workload at N=1: BASELINE.json configs[1] ("C2": Matern-5/2, d=2, n=2048, S=1000
 posterior samples, 100x100 grid).  Multi-GPU: posterior samples are sharded over
-ranks (weak scaling: S per GPU fixed), the per-sample moments are exchanged with
-one NCCL all-gather so each rank reduces a contiguous candidate chunk over ALL
-samples in a fixed order, then (value, index) pairs are all-gathered.
+ranks (--scaling weak: S per GPU fixed; --scaling strong: the same 1000 samples split),
+the per-sample moments are exchanged with one NCCL all-to-all per array so each rank
+reduces a contiguous candidate chunk over ALL samples in a fixed order, then (value,
+index) pairs are all-gathered.  A second leg times BASELINE config 3 (M = 10^6
+candidates x S = 2000 samples, candidates sharded over the ranks) and reports it under
+"c3"; the timed step's own mean / variance are compared with the CPU oracle under "parity".
 
   python bench.py [--gpus N --steps K --warmup W] [--impl reference]
 """
@@ -22,6 +25,12 @@ import subprocess
 import sys
 import threading
 import time
+
+if "reference" in sys.argv[1:]:
+    # torchrun exports OMP_NUM_THREADS=1 to its workers; the reference arm is a CPU
+    # measurement on ALL host cores (rank 0 only), so undo that before NumPy / OpenBLAS load
+    for _k in ("OMP_NUM_THREADS", "OPENBLAS_NUM_THREADS", "MKL_NUM_THREADS"):
+        os.environ[_k] = str(os.cpu_count() or 1)
 
 import numpy as np
 
@@ -44,6 +53,9 @@ def parse():
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"])
     ap.add_argument("--cpu-samples", type=int, default=0, help="samples in the CPU baseline slice (0 = auto)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-c3", action="store_true", help="skip the C3 (candidate-sharded acquisition sweep) leg")
+    ap.add_argument("--c3-candidates", type=int, default=1_000_000)
+    ap.add_argument("--c3-samples", type=int, default=2000)
     return ap.parse_args()
 
 
@@ -52,10 +64,20 @@ def workload(args):
     return syn.config2(n=args.n, S=args.samples, grid=args.grid)
 
 
+def sample_split(args, world):
+    """(S_total, S_local): weak scaling keeps --samples per GPU, strong keeps it in total."""
+    if args.scaling == "weak":
+        return args.samples * world, args.samples
+    if args.samples % world:
+        raise SystemExit(f"--scaling strong needs --samples ({args.samples}) divisible by the rank count ({world})")
+    return args.samples, args.samples // world
+
+
 def config_dict(args, wl, world):
-    return {"workload": f"C2 Matern-5/2 d=2 n={wl.n} S={wl.S}/GPU M={wl.M} "
+    S_total, S_local = sample_split(args, world)
+    return {"workload": f"C2 Matern-5/2 d=2 n={wl.n} S={S_total} ({S_local}/GPU) M={wl.M} "
                         "(gram+cholesky+alpha/mll+trtri+fused predictive+EI argmax)",
-            "n": wl.n, "S_per_gpu": wl.S, "M": wl.M, "d": wl.d, "kernel": wl.kind,
+            "n": wl.n, "S_total": S_total, "S_per_gpu": S_local, "M": wl.M, "d": wl.d, "kernel": wl.kind,
             "sharding": f"samples over {world} rank(s)", "l2": "inputs_exceed_l2"}
 
 
@@ -67,13 +89,48 @@ def cpu_baseline_run(wl, n_samples, repeats=1):
     SciPy, all host threads) on a slice of the same workload."""
     from oracle import gp_oracle as O   # checker / baseline leg only
     hp = {k: (None if v is None else v[:n_samples]) for k, v in wl.hp.items()}
-    best = None
+    best, out = None, None
     for _ in range(repeats):
         t0 = time.perf_counter()
-        O.predict_batched(wl.kind, wl.x, wl.y, wl.x_new, hp, diag_only=True)
+        out = O.predict_batched(wl.kind, wl.x, wl.y, wl.x_new, hp, diag_only=True)
         dt = time.perf_counter() - t0
         best = dt if best is None else min(best, dt)
-    return n_samples * wl.M / best, best
+    return n_samples * wl.M / best, best, out
+
+
+def parity_block(wl, mu_dev, var_dev, mu_o, var_o, argmax_dev):
+    """GPU results of the timed step against the oracle's results for the same samples (the
+    CPU-baseline leg computes them anyway): normwise and elementwise relative errors, and the
+    EI argmax of the mixture over exactly these samples.  Two fp64 evaluations differ by about
+    cond(K) * eps, so the worst sample is also adjudicated against the
+    extended-precision restatement (oracle/ld_oracle.py, 80-bit + iterative refinement) on a
+    candidate subset: ``*_vs_extended`` are the distances of the device and of the LAPACK
+    oracle from that answer."""
+    from oracle import gp_oracle as O, ld_oracle as LDO   # checkers only
+    rel = lambda a, b: float(np.max(np.abs(a - b)) / np.max(np.abs(b)))
+    ew = lambda a, b: float(np.max(np.abs(a - b) / np.maximum(np.abs(b), 1e-300)))
+    mbar, vbar = O.mixture_moments(mu_o, var_o)
+    ei = O.expected_improvement(mbar * (wl.out_std + 1e-8) + wl.out_mean, np.sqrt(vbar) * wl.out_std,
+                                float(wl.y_raw.max()))
+    per_sample = np.max(np.abs(mu_dev - mu_o), axis=1) / np.max(np.abs(mu_o), axis=1)
+    out = {"samples": int(mu_o.shape[0]), "mu_rel": rel(mu_dev, mu_o), "var_rel": rel(var_dev, var_o),
+           "mu_rel_median_sample": float(np.median(per_sample)),
+           "mu_elementwise": ew(mu_dev, mu_o), "var_elementwise": ew(var_dev, var_o),
+           "tolerance": 1e-10, "argmax_equal": bool(int(argmax_dev) == int(np.argmax(ei))),
+           "argmax": int(argmax_dev)}
+    if LDO.has_extended_precision():
+        s = int(np.argmax(per_sample))
+        sub = np.arange(0, wl.M, max(1, wl.M // 200))
+        hp = wl.hp
+        m_ld, v_ld, _ = LDO.predict(wl.kind, wl.x, wl.y, wl.x_new[sub], np.ones(wl.n), np.ones(len(sub)),
+                                    hp["k_scale"][s], hp["k_length"][s], hp["k_noise"][s], hp["k_jitter"][s])
+        m_ld, v_ld = np.asarray(m_ld, float), np.asarray(v_ld, float)
+        out["worst_sample"] = {
+            "index": s, "k_scale": float(hp["k_scale"][s]), "k_noise": float(hp["k_noise"][s]),
+            "mu_device_vs_extended": rel(mu_dev[s][sub], m_ld), "mu_oracle_vs_extended": rel(mu_o[s][sub], m_ld),
+            "var_device_vs_extended": rel(var_dev[s][sub], v_ld), "var_oracle_vs_extended": rel(var_o[s][sub], v_ld),
+            "candidates": int(len(sub))}
+    return out
 
 
 def host_threads():
@@ -89,8 +146,14 @@ def run_reference(args):
     reference itself (JAX/NumPyro) is not importable on this image, so this is
     the oracle port (kind = "port"), on a bounded slice per step."""
     rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
     if rank != 0:
         return
+    try:
+        from threadpoolctl import threadpool_limits
+        threadpool_limits(limits=os.cpu_count() or 1)
+    except Exception:
+        pass
     wl = workload(args)
     ns = args.cpu_samples or max(2, min(8, wl.S))
     from oracle import gp_oracle as O
@@ -107,7 +170,7 @@ def run_reference(args):
         "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * 1e3,
         "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None, "dtype": "f64",
-        "data": "synthetic", "config": config_dict(args, wl, 1),
+        "data": "synthetic", "config": config_dict(args, wl, world),
         "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": "port",
                          "sample": f"{ns} of {wl.S} posterior samples x all {wl.M} candidates per step"},
         "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -211,14 +274,17 @@ def run_ours(args):
         dist.init_process_group("nccl", device_id=dev)
 
     wl = workload(args)
-    S_total = wl.S * world if args.scaling == "weak" else wl.S
-    S_local = wl.S if args.scaling == "weak" else wl.S // world
-    # each rank draws its own shard of hyper-parameter samples (same priors, rank-offset seed)
-    if world > 1:
+    S_total, S_local = sample_split(args, world)
+    if world == 1:
+        hp = wl.hp
+    elif args.scaling == "strong":
+        # the SAME 1000 samples as the 1-GPU run, split into contiguous shards (global order = rank-major)
+        lo, hi = P.shard_range(S_total, world, rank)
+        hp = {k: np.ascontiguousarray(v[lo:hi]) for k, v in wl.hp.items()}
+    else:
+        # weak: every rank draws its own shard of hyper-parameter samples (same priors, rank-offset seed)
         from gpax_b200 import synthetic as syn
         hp = syn.draw_hp(np.random.default_rng(1000 + rank), S_local, 1)
-    else:
-        hp = wl.hp
     n, M, d = wl.n, wl.M, wl.d
     y_max = float(wl.y_raw.max())
 
@@ -245,10 +311,18 @@ def run_ours(args):
     bufW = torch.empty((S_local, n, ld), dtype=torch.float64, device=dev)
     dinv = E.dinv_alloc(S_local, n, dev)
     info = torch.zeros(S_local, dtype=torch.int32, device=dev)
-    mu = torch.empty((S_local, M), dtype=torch.float64, device=dev)
-    var = torch.empty((S_local, M), dtype=torch.float64, device=dev)
+    # per-sample moments in candidate-block-major layout (parallel.block_layout): block r =
+    # [S_local, cnt_r] contiguous, written by one gpx_predict call per block, so the exchange is
+    # one all_to_all_single per array with no packing copy.  world == 1: one block = [S, M].
+    layout = P.block_layout(S_local, M, world)
+    mu = torch.empty(S_local * M, dtype=torch.float64, device=dev)
+    var = torch.empty(S_local * M, dtype=torch.float64, device=dev)
+    my_cnt = layout[rank][2]
+    xbuf = None
+    if world > 1:
+        xbuf = (torch.empty(world * S_local * my_cnt, dtype=torch.float64, device=dev),
+                torch.empty(world * S_local * my_cnt, dtype=torch.float64, device=dev))
     pws = E.predict_ws_alloc(S_local, n, d, dev)
-    ev = {}
 
     def one_step(dev_inputs=None, timed_events=None):
         """The hot path.  dev_inputs: already-resident tensors (kernel-only leg) or
@@ -269,11 +343,15 @@ def run_ours(args):
         E.trtri(bufL, n, dinv, bufW)
         if timed_events is not None:
             timed_events["pred0"].record()
-        E.predict(hpd, di["x"], di["x_new"], bufW, alpha, hpd.jitter, None, 1.0, True, True, mu, var, pws)
+        for eo, co, cnt in layout:                 # one block per reducing rank (one block at N = 1)
+            if cnt:
+                E.predict(hpd, di["x"], di["x_new"][co:co + cnt], bufW, alpha, hpd.jitter, None, 1.0, True, True,
+                          mu[eo:eo + S_local * cnt].view(S_local, cnt),
+                          var[eo:eo + S_local * cnt].view(S_local, cnt), pws)
         if timed_events is not None:
             timed_events["pred1"].record()
         # every candidate is reduced over ALL samples on one rank, in global sample order
-        mu_all, var_all, off = P.exchange_moments(mu, var)
+        mu_all, var_all, off = P.exchange_moments(mu, var, M=M, out=xbuf)
         o_mu, o_sd, o_acq, pv, pi = E.acq_reduce(mu_all, var_all, _cabi.ACQ_EI, 0.0, y_max,
                                                  wl.out_std + 1e-8, wl.out_mean, wl.out_std, off)
         bv, bi = E.argmax_finalize(pv, pi)
@@ -336,6 +414,26 @@ def run_ours(args):
     if world > 1:
         dist.all_reduce(times, op=dist.ReduceOp.MAX)
     t_ms, t_e2e = times.tolist()
+    argmax_c2 = (int(res[4].item()), float(res[3].item()))
+
+    # ---- parity of the timed step's own outputs (rank 0, N = 1): keep what the CPU leg computes ----
+    parity, cpu_line = None, None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        ns = min(args.cpu_samples or 24, wl.S)
+        v, dt, (mu_o, var_o) = cpu_baseline_run(wl, ns)
+        cpu_line = {"value": v, "unit": UNIT, "cores": host_threads(), "kind": "port",
+                    "sample": f"{ns} of {wl.S} posterior samples x all {M} candidates ({dt:.1f} s), "
+                              "SciPy LAPACK oracle"}
+        mu2, var2 = mu.view(S_local, M), var.view(S_local, M)
+        _, _, _, pv, pi = E.acq_reduce(mu2[:ns], var2[:ns], _cabi.ACQ_EI, 0.0, y_max,
+                                       wl.out_std + 1e-8, wl.out_mean, wl.out_std, 0, want_arrays=False)
+        _, bi_ns = E.argmax_finalize(pv, pi)
+        parity = parity_block(wl, mu2[:ns].cpu().numpy(), var2[:ns].cpu().numpy(), mu_o, var_o, bi_ns.item())
+
+    # free the C2 state before the C3 leg
+    del bufL, bufW, dinv, mu, var, pws, xbuf
+    torch.cuda.empty_cache()
+    c3 = None if args.no_c3 else run_c3(args, torch, dist, E, P, _cabi, dev, world, rank)
 
     if rank == 0:
         per_step = t_ms / args.steps
@@ -345,6 +443,7 @@ def run_ours(args):
         chol_tflops = S_local * n**3 / 3.0 / (t_chol * 1e-3) / 1e12
         achieved = pred_flops / (t_pred * 1e-3) / 1e12
         peak = dgemm_sustained
+        traffic, traffic_src = ncu_traffic("predict_ws_kernel", S_local, n, M)
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": per_step, "higher_is_better": True,
@@ -357,24 +456,69 @@ def run_ours(args):
             "roofline": {"kernel": "predict_ws_kernel (fused K* generation + TMA-fed W*K*^T on DMMA + column norms)",
                          "bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
                          "frac": achieved / peak if peak else None,
-                         "traffic": ncu_traffic("predict_ws_kernel", S_local, n, M),
-                         "peak_source": "self-measured cuBLAS DGEMM 8192^3 sustained on this GPU "
+                         "traffic": traffic, "traffic_source": traffic_src,
+                         "peak_source": "self-measured cuBLAS DGEMM 8192^3 sustained on this GPU in this run "
                                         "(MEASURED_PEAKS.json has no FP64 entry); burst = %.1f" % dgemm_burst,
-                         "ms_per_launch": t_pred},
+                         "ms_per_launch": t_pred, "launches_per_step": sum(1 for _, _, c in layout if c)},
             "cholesky": {"tflops": chol_tflops, "ms": t_chol,
                          "frac_of_dgemm": chol_tflops / peak if peak else None,
-                         "flops": "S*n^3/3"},
-            "argmax": {"index": int(res[4].item()), "value": float(res[3].item())},
+                         "flops": "S*n^3/3", "peak": "self-measured cuBLAS DGEMM (as roofline.peak_source)"},
+            "argmax": {"index": argmax_c2[0], "value": argmax_c2[1]},
         }
-        if not args.no_cpu_baseline and world == 1:
-            ns = args.cpu_samples or 24
-            v, dt = cpu_baseline_run(wl, min(ns, wl.S))
-            line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": host_threads(), "kind": "port",
-                                    "sample": f"{min(ns, wl.S)} of {wl.S} posterior samples x all {M} "
-                                              f"candidates ({dt:.1f} s), SciPy LAPACK oracle"}
+        if parity is not None:
+            line["parity"] = parity
+        if cpu_line is not None:
+            line["cpu_baseline"] = cpu_line
+        if c3 is not None:
+            line["c3"] = c3
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
+
+
+def run_c3(args, torch, dist, E, P, _cabi, dev, world, rank):
+    """BASELINE config 3 ("batched EI/UCB acquisition over 1M candidates x 2000 posterior samples,
+    sharded across 8xB200"): the n = 64 posterior of all S samples is replicated (65 MB), the
+    candidates are split into contiguous chunks (global indices via m_offset), each rank runs the
+    fused gpx_predict_acq sweep over its chunk and the 16-byte (value, index) winners are
+    all-gathered over NCCL and finalised on device.  Strong scaling by construction (M fixed).
+    Candidates are uploaded once before the timed sweeps (8 MB)."""
+    from gpax_b200 import synthetic as syn
+    M, S = args.c3_candidates, args.c3_samples
+    wl = syn.config3(S=S, M=M)
+    post = E.Posterior(wl.kind, wl.x, wl.y, wl.hp, device=dev)
+    off, cnt = P.candidate_chunk(M, world, rank)
+    xn = E._dev(wl.x_new[off:off + cnt], dev)
+    y_max = float(wl.y_raw.max())
+    a, b, c = wl.out_std + 1e-8, wl.out_mean, wl.out_std
+    out = {"workload": f"C3 RBF n={wl.n} d={wl.d} S={S} M={M}: fused predictive + acquisition sweep, "
+                       f"candidates sharded over {world} rank(s), posterior replicated",
+           "unit": "candidate x sample pairs/s", "scaling": "strong"}
+    for name, acq, beta in (("ei", _cabi.ACQ_EI, 0.0), ("ucb", _cabi.ACQ_UCB, 10.0)):
+        def sweep():
+            o = post.predict_acq(xn, acq, beta, y_max, a, b, c, m_offset=off, m_tile=8192, want_arrays=False)
+            bv, bi = o[3], o[4]
+            if world > 1:
+                bv, bi = E.argmax_finalize(*P.all_gather_pairs(bv, bi))
+            return bv, bi
+        for _ in range(2):
+            sweep()
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        reps = 3
+        e0, e1 = torch.cuda.Event(True), torch.cuda.Event(True)
+        e0.record()
+        for _ in range(reps):
+            bv, bi = sweep()
+        e1.record()
+        torch.cuda.synchronize()
+        t = torch.tensor([e0.elapsed_time(e1) / reps], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        out[name] = {"ms_per_sweep": t.item(), "pairs_per_s": S * M / t.item() * 1e3,
+                     "argmax_index": int(bi.item()), "argmax_value": float(bv.item())}
+    return out
 
 
 def ncu_traffic(kernel, S, n, M):
@@ -386,10 +530,12 @@ def ncu_traffic(kernel, S, n, M):
         with open(path) as f:
             for row in json.load(f):
                 if row["kernel"] == kernel and (row["S"], row["n"], row["M"]) == (S, n, M):
-                    return row["dram_bytes_read"] + row["dram_bytes_write"]
+                    return (row["dram_bytes_read"] + row["dram_bytes_write"],
+                            "committed ncu --set full capture (profiles/roofline_traffic.json: %s), "
+                            "not a measurement of this run" % row.get("capture", "r01"))
     except (OSError, ValueError, KeyError):
         pass
-    return None
+    return None, None
 
 
 def _hpd_from_device(E, kind, d, di, dev):

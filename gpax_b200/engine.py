@@ -77,6 +77,9 @@ class HyperParams:
         jitter = np.full(self.S, 1e-6) if jitter is None else np.asarray(jitter, float).reshape(-1)
         noise = np.broadcast_to(noise, (self.S,)) if noise.size == 1 else noise
         jitter = np.broadcast_to(jitter, (self.S,)) if jitter.size == 1 else jitter
+        for name, arr in (("k_noise", noise), ("k_jitter", jitter)):
+            if arr.shape != (self.S,):        # the kernels index these by sample: never let a short array through
+                raise ValueError(f"{name} must have 1 or S={self.S} entries, got {arr.size}")
         self.scale = _dev(scale, dev)
         self.length = _dev(length, dev)
         self.period = _dev(period, dev)

@@ -54,11 +54,18 @@ class Prior:
 
     @property
     def _params(self):
+        """``Parameter`` attributes whose name starts with the prefix, declared either on
+        the instance or on the class (the reference's attrs ``field(default=Parameter(...))``
+        pattern, examples/04_Structured_GP.ipynb cell 10), in declaration order."""
         out = {}
+        for klass in reversed(type(self).__mro__):
+            for key, obj in vars(klass).items():
+                if key.startswith(self.attribute_prefix) and isinstance(obj, Parameter):
+                    out[key] = obj
         for key, obj in vars(self).items():
             if key.startswith(self.attribute_prefix) and isinstance(obj, Parameter):
                 out[key] = obj
-        return out
+        return {k: getattr(self, k) for k in out if isinstance(getattr(self, k), Parameter)}
 
     @property
     def params(self):
@@ -104,7 +111,8 @@ class Kernel(Prior):
         return self._kernel_function(x1, x2, **params)
 
     # -- device evaluation --------------------------------------------------
-    def _gram(self, x1, x2, k_scale, k_length, k_noise, k_jitter, apply_noise, k_period=None):
+    def _gram(self, x1, x2, k_scale, k_length, k_noise, k_jitter, apply_noise, k_period=None,
+              noise_is_vector=None):
         from . import engine as E   # deferred: importing the declarations needs no GPU
 
         dev = E._require_cuda()
@@ -114,9 +122,18 @@ class Kernel(Prior):
         x2 = x2.reshape(len(x2), -1)
         if x1.shape[1] != x2.shape[1]:
             raise ValueError(f"x1 and x2 differ in dimension: {x1.shape} vs {x2.shape}")
-        batched = np.ndim(k_scale) > 0
-        hp = {"k_scale": np.atleast_1d(np.asarray(k_scale, float)), "k_jitter": k_jitter}
+        # size-1 arrays are scalars, exactly as NumPy/JAX broadcasting treats them in the
+        # reference's formulas; only k_scale with more than one entry opens a sample axis
+        ks = np.asarray(k_scale, float)
+        if ks.size == 1:
+            ks = ks.reshape(())
+        if ks.ndim > 1:
+            raise ValueError(f"k_scale must be a scalar or [S], got shape {ks.shape}")
+        batched = ks.ndim == 1
+        hp = {"k_scale": np.atleast_1d(ks)}
         S = hp["k_scale"].shape[0]
+        kj = np.asarray(k_jitter, float)
+        hp["k_jitter"] = kj.reshape(()) if kj.size == 1 else kj
         kl = np.asarray(k_length, float)
         hp["k_length"] = kl.reshape(S, -1) if batched else kl.reshape(1, -1)
         if k_period is not None:
@@ -125,15 +142,27 @@ class Kernel(Prior):
         # the reference adds the diagonal only for equal shapes (gpax/kernels.py:124,145,166)
         add_diag = bool(apply_noise) and x1.shape == x2.shape
         kn = np.asarray(k_noise, float)
+        if kn.size == 1:
+            kn = kn.reshape(())
         noise_vec = None
-        per_sample = kn.ndim == 0 or (batched and kn.ndim == 1 and kn.shape[0] == S)
-        if per_sample:
+        n1 = x1.shape[0]
+        if noise_is_vector is None:
+            # un-batched call (the reference's own signature): a length-n vector is per-point
+            # noise (y_std**2, gpax/gp.py:289-290).  Batched call: [S] is per-sample; when S == n
+            # the two readings collide, so the caller has to say which one it means.
+            if kn.ndim == 1 and batched and kn.shape[0] == S and S == n1 and add_diag:
+                raise ValueError(f"k_noise of length {S} is ambiguous (S == n == {S}): pass "
+                                 "noise_is_vector=True (per point) or False (per sample)")
+            noise_is_vector = kn.ndim == 1 and not (batched and kn.shape[0] == S)
+        if kn.ndim == 0 or not noise_is_vector:
+            if kn.ndim == 1 and kn.shape[0] != S:
+                raise ValueError(f"per-sample k_noise has {kn.shape[0]} entries for {S} samples")
             hp["k_noise"] = kn
-        elif kn.ndim == 1 and kn.shape[0] == x1.shape[0]:
+        elif kn.ndim == 1 and kn.shape[0] == n1:
             noise_vec = kn              # heteroscedastic y_std**2 (gpax/gp.py:289-290)
         else:
             raise ValueError(f"k_noise of shape {kn.shape} matches neither the sample axis "
-                             f"({S}) nor the number of points ({x1.shape[0]})")
+                             f"({S}) nor the number of points ({n1})")
         hpd = E.HyperParams(self.kind, x1.shape[1], hp, dev)
         d1, d2 = E._dev(x1, dev), E._dev(x2, dev)
         nz = None if noise_vec is None else E._dev(noise_vec, dev)
@@ -153,8 +182,9 @@ class ScaleKernel(Kernel):
                                else k_length, "k_length")
 
     def _kernel_function(self, x1, x2, k_scale, k_length, k_noise=0.0, k_jitter=1.0e-6,
-                         apply_noise=True):
-        return self._gram(x1, x2, k_scale, k_length, k_noise, k_jitter, apply_noise)
+                         apply_noise=True, noise_is_vector=None):
+        return self._gram(x1, x2, k_scale, k_length, k_noise, k_jitter, apply_noise,
+                          noise_is_vector=noise_is_vector)
 
 
 class RBFKernel(ScaleKernel):
@@ -180,5 +210,6 @@ class PeriodicKernel(ScaleKernel):
                                else k_period, "k_period")
 
     def _kernel_function(self, x1, x2, k_scale, k_length, k_period, k_noise=0.0,
-                         k_jitter=1.0e-6, apply_noise=True):
-        return self._gram(x1, x2, k_scale, k_length, k_noise, k_jitter, apply_noise, k_period)
+                         k_jitter=1.0e-6, apply_noise=True, noise_is_vector=None):
+        return self._gram(x1, x2, k_scale, k_length, k_noise, k_jitter, apply_noise, k_period,
+                          noise_is_vector=noise_is_vector)

@@ -8,8 +8,10 @@ gpax/state.py:60-70).  The path shards naturally:
 * for the acquisition reduction every candidate's sum over ALL samples must be
   accumulated on one rank in the fixed order ``s = 0..S-1`` so that the result
   -- and therefore the argmax -- is bit-identical for any rank count.  The
-  per-sample moments ``mu, var [S_local, M]`` are all-gathered (rank-major =
-  global sample order) and each rank reduces one contiguous chunk of candidates;
+  per-sample moments ``mu, var [S_local, M]`` are exchanged with one
+  ``all_to_all_single`` per array (each candidate block travels only to the rank
+  that reduces it; rank-major = global sample order) and each rank reduces one
+  contiguous chunk of candidates;
 * the per-rank winners ``(value, global index)`` (16 bytes) are all-gathered and
   reduced with the same first-max rule (lowest index wins ties, NaN is maximal;
   ``vals.argmax()`` gpax/acquisition.py:214).
@@ -48,22 +50,56 @@ def candidate_chunk(M: int, world: int, rank: int):
     return off, max(0, min(mc, int(M) - off))
 
 
-def exchange_moments(mu: torch.Tensor, var: torch.Tensor, group=None):
-    """All-gather the per-sample moments of every rank and return this rank's
-    candidate chunk over ALL samples: ``(mu_all[S_total, m], var_all[S_total, m],
-    offset)`` with samples in global (rank-major) order.  Every rank must hold the
-    same ``S_local``."""
+def block_layout(S_local: int, M: int, world: int):
+    """Candidate-block-major layout of a rank's per-sample moments: block ``r`` (the candidates
+    rank ``r`` will reduce, ``candidate_chunk(M, world, r)``) is a contiguous ``[S_local, cnt_r]``
+    matrix at element offset ``S_local * off_r`` of one flat buffer.  Returns
+    ``[(elem_offset, cand_offset, cnt)] * world``."""
+    out = []
+    for r in range(world):
+        off, cnt = candidate_chunk(M, world, r)
+        out.append((S_local * off, off, cnt))
+    return out
+
+
+def exchange_moments(mu: torch.Tensor, var: torch.Tensor, M: int = None, group=None, out=None):
+    """Hand every rank the per-sample moments of ITS candidate chunk over ALL samples:
+    returns ``(mu_all[S_total, m], var_all[S_total, m], offset)`` with samples in global
+    (rank-major) order.  Every rank must hold the same ``S_local``.
+
+    ``mu`` / ``var`` are either ``[S_local, M]`` matrices (copied into the block layout here) or
+    flat buffers already in :func:`block_layout` (what ``gpx_predict`` writes when it is called
+    once per candidate block; pass ``M``).  One ``all_to_all_single`` per array moves
+    ``S_local * M * 8`` bytes per rank -- each block goes only to the rank that reduces it --
+    instead of all-gathering the full ``[S_total, M]`` array everywhere."""
     world, rank = world_info()
     if world == 1:
+        if mu.dim() == 1:
+            return mu.view(-1, M), var.view(-1, M), 0
         return mu, var, 0
-    S_local, M = mu.shape
-    off, cnt = candidate_chunk(M, world, rank)
-    out = []
-    for t in (mu, var):
-        buf = torch.empty((world * S_local, M), dtype=t.dtype, device=t.device)
-        dist.all_gather_into_tensor(buf, t.contiguous(), group=group)   # concatenated along dim 0
-        out.append(buf[:, off:off + cnt].contiguous())
-    return out[0], out[1], off
+    if mu.dim() == 2:
+        S_local, M = mu.shape
+        lay = block_layout(S_local, M, world)
+        packed = []
+        for t in (mu, var):
+            flat = torch.empty(S_local * M, dtype=t.dtype, device=t.device)
+            for eo, co, cnt in lay:
+                flat[eo:eo + S_local * cnt].view(S_local, cnt).copy_(t[:, co:co + cnt])
+            packed.append(flat)
+        mu, var = packed
+    else:
+        S_local = mu.numel() // M
+        lay = block_layout(S_local, M, world)
+    off, cnt = lay[rank][1], lay[rank][2]
+    in_splits = [S_local * c for _, _, c in lay]
+    out_splits = [S_local * cnt] * world
+    res = []
+    for i, t in enumerate((mu, var)):
+        buf = out[i] if out is not None else torch.empty(world * S_local * cnt, dtype=t.dtype, device=t.device)
+        dist.all_to_all_single(buf, t, output_split_sizes=out_splits, input_split_sizes=in_splits,
+                               group=group)
+        res.append(buf.view(world * S_local, cnt))
+    return res[0], res[1], off
 
 
 def all_gather_pairs(best_val: torch.Tensor, best_idx: torch.Tensor, group=None):

@@ -341,9 +341,9 @@ def test_exp_sqrt_vec_accuracy_through_gram_free_path(cuda):
 
 
 def test_c4_single_large_matrix_mll_and_grad(cuda):
-    """BASELINE config C4: RBF, n = 16384, S = 1 (right-looking schedule).  No CPU oracle
-    finishes at this size in seconds, so the checks are (i) the MLL against an independent
-    device factorisation (cuSOLVER through torch.linalg.cholesky) at 1e-10 relative,
+    """BASELINE config C4: RBF, n = 16384, S = 1 (right-looking schedule).  Checks: (i) the MLL
+    against the CPU oracle (LAPACK) and against an independent device factorisation (cuSOLVER
+    through torch.linalg.cholesky) at 1e-10 relative,
     (ii) L L^T v = K v and W L v = v on random vectors, (iii) the analytic gradient against
     central differences of our own MLL along a random direction in log-theta."""
     import torch
@@ -377,6 +377,9 @@ def test_c4_single_large_matrix_mll_and_grad(cuda):
     got = float(post.mll.item())
     assert abs(got - ref) / abs(ref) < 1e-10
     del K, Lr, Kv
+    # and against the CPU oracle itself (LAPACK dpotrf through SciPy, ~15 s on 8 host threads)
+    ref_cpu = O.mll("rbf", x, y, np.ones(n), theta["k_scale"], theta["k_length"], theta["k_noise"], 1e-6)
+    assert abs(got - ref_cpu) / abs(ref_cpu) < 1e-10
     g = post.grad()
     gvec = np.array([float(g["k_scale"].item()), float(g["k_length"].item()), float(g["k_noise"].item())])
     names = ["k_scale", "k_length", "k_noise"]
@@ -421,6 +424,107 @@ def test_c1_full_size_vs_oracle(cuda):
         torch.cuda.synchronize()
         assert _rel(o_acq.cpu().numpy(), ref) < 1e-8
         assert int(bi.item()) == O.first_argmax(ref)
+
+
+def _elementwise(a, b):
+    return float(np.max(np.abs(a - b) / np.maximum(np.abs(b), 1e-300)))
+
+
+def _full_size_vs_oracle(cuda, wl, S_sub, elementwise_var_bound):
+    """Shared body of the C2 / C5 full-size parity tests: the first ``S_sub`` posterior samples of
+    the BASELINE workload, ALL candidates, through the same C-ABI calls bench.py times, against
+    ``oracle.predict_batched(diag_only=True)``.  Normwise 1e-10 for mean / variance / MLL (the
+    north_star tolerance), the variance additionally elementwise against a stated
+    conditioning-limited bound (BASELINE.md asks for both), EI / UCB argmax index bit-exact
+    (fused sweep and two-stage path)."""
+    import torch
+    from gpax_b200 import engine as E, _cabi
+    hp = {k: v[:S_sub] for k, v in wl.hp.items() if k.startswith("k_")}
+    mt = None if wl.m_train is None else wl.m_train[:S_sub]
+    mn = None if wl.m_new is None else wl.m_new[:S_sub]
+    post = E.Posterior(wl.kind, wl.x, wl.y, hp, m_train=mt, device=cuda)
+    mu, var = post.predict(wl.x_new, m_new=mn)
+    torch.cuda.synchronize()
+    assert int(post.info.abs().max()) == 0
+    mu_o, var_o = O.predict_batched(wl.kind, wl.x, wl.y, wl.x_new, hp, m_train=mt, m_new=mn,
+                                    diag_only=True)
+    mu_d, var_d = mu.cpu().numpy(), var.cpu().numpy()
+    assert _rel(mu_d, mu_o) < 1e-10
+    assert _rel(var_d, var_o) < 1e-10
+    # elementwise: var = k** - ||v||^2 cancels near training points, so two correct fp64
+    # evaluations differ by ~ cond * eps * k_scale / var there (SURVEY.md H1)
+    ew = _elementwise(var_d, var_o)
+    assert ew < elementwise_var_bound, ew
+    mll_o = np.array([O.mll(wl.kind, wl.x, wl.y, np.ones(wl.n) if mt is None else mt[s],
+                            hp["k_scale"][s], hp["k_length"][s], hp["k_noise"][s], hp["k_jitter"][s],
+                            None if hp.get("k_period") is None else hp["k_period"][s])
+                      for s in range(S_sub)])
+    assert np.max(np.abs(post.mll.cpu().numpy() - mll_o) / np.abs(mll_o)) < 1e-10
+    y_max = float(wl.y_raw.max())
+    a, b, c = wl.out_std + 1e-8, wl.out_mean, wl.out_std
+    mbar, vbar = O.mixture_moments(mu_o, var_o)
+    mu_u, sd_u = mbar * a + b, np.sqrt(vbar) * c
+    for acq, beta in ((_cabi.ACQ_EI, 0.0), (_cabi.ACQ_UCB, 10.0)):
+        ref = O.acquisition(acq, mu_u, sd_u, beta, y_max)
+        _, _, o_acq, pv, pi = E.acq_reduce(mu, var, acq, beta, y_max, a, b, c)
+        _, bi = E.argmax_finalize(pv, pi)
+        f_mu, f_sd, f_acq, fbv, fbi = post.predict_acq(wl.x_new, acq, beta=beta, y_max=y_max, mu_scale=a,
+                                                       mu_shift=b, sd_scale=c, m_new=mn)
+        torch.cuda.synchronize()
+        assert _rel(o_acq.cpu().numpy(), ref) < 1e-8
+        assert int(bi.item()) == O.first_argmax(ref)
+        assert int(fbi.item()) == O.first_argmax(ref)
+        np.testing.assert_array_equal(f_acq.cpu().numpy(), o_acq.cpu().numpy())
+    return ew
+
+
+def test_c2_full_size_vs_oracle(cuda):
+    """BASELINE config C2 at ITS OWN size (Matern-5/2, d=2, n=2048, 100x100 grid): the headline
+    kernel variant at the headline shape (predict_ws_kernel<MATERN52, WN=1, DMAX=2>, R = 512, 128
+    k-slices, 4 row blocks), 4 of the 1000 samples so the oracle finishes in seconds."""
+    from gpax_b200 import synthetic as syn
+    wl = syn.config2()            # the bench workload itself; first 4 of its 1000 samples
+    _full_size_vs_oracle(cuda, wl, 4, 1e-5)
+
+
+def test_c2_ill_conditioned_samples_adjudicated(cuda):
+    """The two worst-conditioned of C2's first 24 samples (k_noise at the 1e-4 floor with
+    k_scale 4.3; k_scale 11 with k_noise 6.7e-4: cond(K) ~ 1e8).  Here LAPACK -- the reference's
+    own CPU backend -- is itself 3e-10 away from the exact posterior mean, so "1e-10 against the
+    fp64 oracle" is not a meaningful bar; the bar is the extended-precision answer
+    (oracle/ld_oracle.py): the device must be within 1e-10 of it or at least as close as LAPACK
+    (x2 slack), normwise, for mean and variance."""
+    import torch
+    from gpax_b200 import engine as E, synthetic as syn
+    from oracle import ld_oracle as LDO
+    if not LDO.has_extended_precision():
+        pytest.skip("numpy.longdouble is not x87 extended precision on this host")
+    wl = syn.config2()
+    idx = [5, 13]
+    hp = {k: v[idx] for k, v in wl.hp.items()}
+    sub = np.arange(0, wl.M, 50)
+    post = E.Posterior(wl.kind, wl.x, wl.y, hp, device=cuda)
+    mu, var = post.predict(wl.x_new[sub])
+    torch.cuda.synchronize()
+    assert int(post.info.abs().max()) == 0
+    mu_o, var_o = O.predict_batched(wl.kind, wl.x, wl.y, wl.x_new[sub], hp, diag_only=True)
+    for q in range(len(idx)):
+        m_ld, v_ld, conv = LDO.predict(wl.kind, wl.x, wl.y, wl.x_new[sub], np.ones(wl.n), np.ones(len(sub)),
+                                       hp["k_scale"][q], hp["k_length"][q], hp["k_noise"][q], hp["k_jitter"][q])
+        assert conv < 1e-12                      # the refinement converged
+        m_ld, v_ld = np.asarray(m_ld, float), np.asarray(v_ld, float)
+        e_dev, e_lap = _rel(mu[q].cpu().numpy(), m_ld), _rel(mu_o[q], m_ld)
+        assert e_dev < max(1e-10, 2 * e_lap), (idx[q], e_dev, e_lap)
+        v_dev, v_lap = _rel(var[q].cpu().numpy(), v_ld), _rel(var_o[q], v_ld)
+        assert v_dev < max(1e-10, 2 * v_lap), (idx[q], v_dev, v_lap)
+
+
+def test_c5_full_size_vs_oracle(cuda):
+    """BASELINE config C5 at its own size (Periodic + piecewise power-law mean, d=3, n=1024,
+    M=10^4, per-sample m_train / m_new)."""
+    from gpax_b200 import synthetic as syn
+    wl = syn.config5()
+    _full_size_vs_oracle(cuda, wl, 4, 1e-5)
 
 
 def test_c3_full_size_acquisition_sweep(cuda):

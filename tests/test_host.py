@@ -116,6 +116,15 @@ full_mu = np.concatenate([np.random.default_rng(100 + r).normal(size=(S_local, M
 o, c = P.candidate_chunk(M, world, rank)
 assert off == o and mu_all.shape == (world * S_local, c)
 np.testing.assert_array_equal(mu_all.numpy(), full_mu[:, o:o + c])
+# the same exchange from buffers already in the candidate-block-major layout (what bench.py's
+# per-block gpx_predict calls write): no packing copy
+lay = P.block_layout(S_local, M, world)
+fm, fv = np.empty(S_local * M), np.empty(S_local * M)
+for eo, co, cnt in lay:
+    fm[eo:eo + S_local * cnt] = mu[:, co:co + cnt].ravel(); fv[eo:eo + S_local * cnt] = var[:, co:co + cnt].ravel()
+mu_b, var_b, off_b = P.exchange_moments(torch.from_numpy(fm), torch.from_numpy(fv), M=M)
+assert off_b == off
+np.testing.assert_array_equal(mu_b.numpy(), mu_all.numpy()); np.testing.assert_array_equal(var_b.numpy(), var_all.numpy())
 # fixed-order reduction of the chunk (stand-in for gpx_acq_reduce) + winner exchange
 mbar, vbar = O.mixture_moments_device_order(mu_all.numpy(), var_all.numpy())
 acq = O.ucb(mbar, np.sqrt(vbar), 10.0)

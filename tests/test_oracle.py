@@ -259,3 +259,24 @@ def test_rng_key_chain():
     np.random.seed(0)
     assert k1 == int(np.random.randint(0, 2**32 - 1))
     assert O.next_rng_key(k1) != k1
+
+
+@pytest.mark.parametrize("name", ["sinusoid_rbf", "sinusoid_matern", "c1_small"])
+def test_extended_precision_adjudicator_matches_mpmath(name):
+    """oracle/ld_oracle.py (80-bit + iterative refinement; the adjudicator used at n = 2048)
+    against the stored 50-digit mpmath results at small n: it must be at least 100x closer to
+    mpmath than the fp64 oracle's own conditioning-limited error, and within 1e-14."""
+    from oracle import ld_oracle as LDO
+    if not LDO.has_extended_precision():
+        pytest.skip("numpy.longdouble is not x87 extended precision on this host")
+    z, hp = _load(name)
+    kind = str(z["kind"])
+    xn = z["x_new"][:40]
+    for s in range(z["mp_mu"].shape[0]):
+        m, v, conv = LDO.predict(kind, z["x"], z["y"], xn, np.ones(len(z["x"])), np.ones(len(xn)),
+                                 hp["k_scale"][s], hp["k_length"][s], hp["k_noise"][s], hp["k_jitter"][s],
+                                 observation_noise=bool(z["observation_noise"]))
+        assert conv < 1e-13
+        e_m = _rel(np.asarray(m, float), z["mp_mu"][s])
+        e_v = _rel(np.asarray(v, float), z["mp_var"][s])
+        assert e_m < 1e-14 and e_v < 1e-13, (s, e_m, e_v)
