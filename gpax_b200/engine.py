@@ -134,32 +134,42 @@ def trtri(L, n, dinv, W=None):
     return W
 
 
-def mll(L, n, dinv, resid, want_alpha=True, ws=None):
-    """resid: [n] (shared) or [S, n]."""
+def mll(L, n, dinv, resid, want_alpha=True, ws=None, alpha=None, val=None):
+    """resid: [n] (shared) or [S, n].  ``alpha`` / ``val``: optional preallocated outputs."""
     S, _, ldl = L.shape
     dev = L.device
     if ws is None:
         ws = torch.empty(max(1, lib.gpx_mll_ws_bytes(S, n) // 8), dtype=F64, device=dev)
     stride = 0 if resid.dim() == 1 else n
-    alpha = torch.empty((S, n), dtype=F64, device=dev) if want_alpha else None
-    val = torch.empty(S, dtype=F64, device=dev)
+    if alpha is None and want_alpha:
+        alpha = torch.empty((S, n), dtype=F64, device=dev)
+    if val is None:
+        val = torch.empty(S, dtype=F64, device=dev)
     check(lib.gpx_mll(S, n, _ptr(L), ldl, _ptr(dinv), _ptr(resid), stride, _ptr(alpha),
                       _ptr(val), _ptr(ws), _stream()), "gpx_mll")
     return val, alpha
 
 
-def mll_grad(hpd: HyperParams, x, W, alpha):
+def mll_grad_ws_alloc(S, n, d, dev):
+    return torch.empty(max(1, lib.gpx_mll_grad_ws_bytes(S, n, d) // 8), dtype=F64, device=dev)
+
+
+def mll_grad(hpd: HyperParams, x, W, alpha, out=None, ws=None):
+    """``out``: optional dict of preallocated ``k_scale [S]``, ``k_length [S, dl]``,
+    ``k_noise [S]`` (and ``k_period [S, dp]``) tensors."""
     S, n, ldw = W.shape[0], x.shape[0], W.shape[2]
     dev = W.device
-    ws = torch.empty(max(1, lib.gpx_mll_grad_ws_bytes(S, n, hpd.d) // 8), dtype=F64, device=dev)
-    out = {
-        "k_scale": torch.empty(S, dtype=F64, device=dev),
-        "k_length": torch.empty((S, hpd.dl), dtype=F64, device=dev),
-        "k_noise": torch.empty(S, dtype=F64, device=dev),
-    }
-    dper = None
-    if hpd.dp:
-        dper = out["k_period"] = torch.empty((S, hpd.dp), dtype=F64, device=dev)
+    if ws is None:
+        ws = mll_grad_ws_alloc(S, n, hpd.d, dev)
+    if out is None:
+        out = {
+            "k_scale": torch.empty(S, dtype=F64, device=dev),
+            "k_length": torch.empty((S, hpd.dl), dtype=F64, device=dev),
+            "k_noise": torch.empty(S, dtype=F64, device=dev),
+        }
+        if hpd.dp:
+            out["k_period"] = torch.empty((S, hpd.dp), dtype=F64, device=dev)
+    dper = out.get("k_period") if hpd.dp else None
     check(lib.gpx_mll_grad(C.byref(hpd.kp), S, n, _ptr(x), _ptr(W), ldw, _ptr(alpha),
                            _ptr(out["k_scale"]), _ptr(out["k_length"]), _ptr(dper),
                            _ptr(out["k_noise"]), _ptr(ws), _stream()), "gpx_mll_grad")

@@ -13,8 +13,16 @@ Differences that follow from the scope:
   Cholesky factor (row N1, "next"); until that has its own kernels it is
   assembled on the device from ``gpx_gram`` outputs with cuBLAS/cuSOLVER calls
   through torch and is limited to modest ``M``.  Pass ``draw=False`` to skip.
-* ``fit`` runs the multi-chain HMC of ``gpax_b200.infer`` (NUTS is row N2).
-* ``use_cholesky`` is accepted and ignored: the device path always factorises.
+* ``fit`` runs the samplers of ``gpax_b200.infer`` (NUTS by default) over the kernel
+  AND mean (``m_*``) parameters.
+* ``use_cholesky``: the device path always works from the Cholesky factor.  The
+  reference's DEFAULT is the ``jnp.linalg.inv`` branch (gpax/gp.py:129,303-310),
+  which computes the same quantities; the two agree to ~cond(K)*eps (DESIGN.md
+  section 2), so the flag is accepted with either value and recorded in
+  ``metadata["solver"]``.
+* Learnable mean parameters of an UN-fit model are drawn from their priors next to
+  the kernel parameters (the reference passes the Distribution objects themselves
+  to the mean function there, gpax/gp.py:328, which only works for constants).
 """
 from __future__ import annotations
 
@@ -143,6 +151,9 @@ class GaussianProcess:
         self.hp_samples, self.gp_samples = hp_samples, gp_samples
         self.metadata = {} if metadata is None else metadata
         self.use_cholesky, self.mean = use_cholesky, mean
+        self.metadata.setdefault(
+            "solver", "device Cholesky (gpx_potrf_batched); use_cholesky=%s accepted, the reference's "
+                      "inv branch agrees to ~cond(K)*eps" % use_cholesky)
         self._is_fit = False
         self._posterior_cache = None
 
@@ -184,6 +195,8 @@ class GaussianProcess:
 
     def _get_hp_samples_from_prior(self, rng, fast):
         hp = self.kernel.sample_parameters(rng, self.hp_samples)
+        for k in self.mean.learnable():          # see the module docstring
+            hp[k] = self.mean._params[k].draw(rng, self.hp_samples)
         return (self._median(hp), 1) if fast else (hp, self.hp_samples)
 
     def _get_hp_samples_from_posterior(self, fast):
@@ -195,10 +208,23 @@ class GaussianProcess:
         return self._get_hp_samples_from_posterior(fast)
 
     # -- device moments ------------------------------------------------------
-    def _mean_values(self, x):
-        if self.mean._params:
-            raise NotImplementedError("learnable mean parameters are not built yet (row N2)")
-        return np.broadcast_to(np.asarray(self.mean(x), float), (len(x),)).copy()
+    @staticmethod
+    def _n_samples(hp):
+        return len(np.atleast_1d(hp["k_scale"]))
+
+    def _mean_values(self, x, hp):
+        """Mean function per hyper-parameter sample (gpax/gp.py:266-278: the ``m_*`` entries of
+        the sample dict go to the mean, the ``k_*`` entries to the kernel): ``[S, N]``, or
+        ``[1, N]`` when no mean parameter is sampled."""
+        return self.mean.evaluate(x, hp, self._n_samples(hp))
+
+    def _m_new_kw(self, x_new_t, hp):
+        """Mean at the new points as the argument ``gpx_predict`` wants: one constant, or [S, M]."""
+        m_new = self._mean_values(x_new_t, hp)
+        if m_new.shape[0] == 1 and np.all(m_new == m_new[0, 0]):
+            return {"m_const": float(m_new[0, 0])}
+        S = self._n_samples(hp)
+        return {"m_new": np.ascontiguousarray(np.broadcast_to(m_new, (S, m_new.shape[1])))}
 
     def _posterior(self, hp):
         """Cached device factorisation for this exact set of samples."""
@@ -207,7 +233,7 @@ class GaussianProcess:
         key = tuple((k, np.asarray(v).tobytes()) for k, v in sorted(hp.items()))
         if self._posterior_cache is None or self._posterior_cache[0] != key:
             post = E.Posterior(self.kernel.kind, self.x_transformed, self.y_transformed, hp,
-                               m_train=self._mean_values(self.x_transformed)[None, :],
+                               m_train=self._mean_values(self.x_transformed, hp),
                                y_std=self.y_std_transformed)
             bad = post.info.cpu().numpy()
             if bad.any():
@@ -223,23 +249,20 @@ class GaussianProcess:
 
         from . import engine as E
 
-        x_new_t = np.asarray(x_new_t, float).reshape(len(x_new_t), -1)
-        m_new = self._mean_values(x_new_t)
+        x_new_2d = np.asarray(x_new_t, float).reshape(len(x_new_t), -1)
         if self.x is None:
             # unconditioned prior (gpax/gp.py:211-243): stationary kernel, diagonal only
             dev = E._require_cuda()
-            S = len(np.atleast_1d(hp["k_scale"]))
+            S = self._n_samples(hp)
+            m_new = self._mean_values(x_new_t, hp)
             noise = np.asarray(hp["k_noise"], float).reshape(-1) if self.observation_noise else 0.0
             var = np.asarray(hp["k_scale"], float).reshape(-1) + noise \
                 + np.asarray(hp["k_jitter"], float).reshape(-1)
-            mu = E._dev(np.broadcast_to(m_new, (S, len(m_new))).copy(), dev)
+            mu = E._dev(np.broadcast_to(m_new, (S, m_new.shape[1])).copy(), dev)
             return mu, E._dev(np.broadcast_to(var[:, None], mu.shape).copy(), dev), None
         post = self._posterior(hp)
-        if np.all(m_new == m_new[0]):            # constant mean: scalar argument of gpx_predict
-            kw = {"m_const": float(m_new[0])}
-        else:                                    # gpx_predict takes m_new as [S, M]
-            kw = {"m_new": np.broadcast_to(m_new, (post.S, len(m_new))).copy()}
-        mu, var = post.predict(x_new_t, observation_noise=self.observation_noise, **kw)
+        mu, var = post.predict(x_new_2d, observation_noise=self.observation_noise,
+                               **self._m_new_kw(x_new_t, hp))
         return mu, var, post
 
     def _draw(self, rng_seed, x_new_t, hp, mu, post):
@@ -293,7 +316,7 @@ class GaussianProcess:
         key, rng = state.get_rng_key()
         hp, _ = self._hp_for(rng, fast)
         mu, var, post = self._moments_device(x_new_t, hp)
-        sd = var.clamp(min=0.0).sqrt()
+        sd = var.sqrt()          # un-clamped like gpax/gp.py:338: a negative variance gives NaN
         y = None
         if draw:
             y = self._draw(key, x_new_t, hp, mu, post).cpu().numpy()
@@ -317,13 +340,9 @@ class GaussianProcess:
         a, b, c = _affine_of(self.output_transform)
         if self.x is not None:
             # conditioned model: one fused gpx_predict_acq sweep, no [S, M] moment buffers
-            x_new_t = np.asarray(x_new_t, float).reshape(len(x_new_t), -1)
             post = self._posterior(hp)
-            m_new = self._mean_values(x_new_t)
-            if np.all(m_new == m_new[0]):
-                kw = {"m_const": float(m_new[0])}
-            else:
-                kw = {"m_new": np.broadcast_to(m_new, (post.S, len(m_new))).copy()}
+            kw = self._m_new_kw(x_new_t, hp)
+            x_new_t = np.asarray(x_new_t, float).reshape(len(x_new_t), -1)
             o_mu, o_sd, o_acq, bv, bi = post.predict_acq(
                 x_new_t, acq, beta=beta, y_max=y_max, mu_scale=a, mu_shift=b, sd_scale=c,
                 observation_noise=self.observation_noise, want_arrays=want_arrays, **kw)
@@ -353,30 +372,38 @@ class ExactGP(GaussianProcess):
     def __init__(self, kernel, x=None, y=None, y_std=None, observation_noise=False,
                  hp_samples=100, gp_samples=10, input_transform="default",
                  output_transform="default", metadata=None, use_cholesky=False, mean=None,
-                 num_warmup=2000, num_chains=1, chain_method="vectorized",
+                 mcmc=None, num_warmup=2000, num_chains=1, chain_method="sequential",
                  mcmc_run_kwargs=None):
         super().__init__(kernel, x, y, y_std, observation_noise, hp_samples, gp_samples,
                          input_transform, output_transform, metadata, use_cholesky, mean)
         _check_pos_int("num_warmup", num_warmup)
         _check_pos_int("num_chains", num_chains)
         _check("chain_method", chain_method, str)
+        if chain_method not in ("sequential", "vectorized", "parallel"):
+            raise ValueError("chain_method must be 'sequential', 'vectorized' or 'parallel'")
         self.num_warmup, self.num_chains = num_warmup, num_chains
+        # NumPyro's options (gpax/gp.py:509,521): "sequential" (the reference default) runs the
+        # chains one after another, "vectorized" / "parallel" advance them in lock-step as one
+        # batch of factorisations -- the fast choice on the device
         self.chain_method = chain_method
         self.mcmc_run_kwargs = {} if mcmc_run_kwargs is None else dict(mcmc_run_kwargs)
-        self.mcmc = None
+        self.mcmc = mcmc
+        if mcmc is not None:                     # a model re-created around existing sampler output
+            self._is_fit = True
 
     def fit(self):
-        """Hamiltonian Monte Carlo over the kernel hyper-parameters.  As in the
-        reference's ``_gp_prior`` (gpax/gp.py:133-151) the likelihood uses the
-        sampled ``k_noise``; ``y_std`` only enters at prediction time."""
+        """NUTS over the kernel and mean hyper-parameters (gpax/gp.py:512-534).  As in the
+        reference's ``_gp_prior`` (gpax/gp.py:133-151) the likelihood uses the sampled
+        ``k_noise``; ``y_std`` only enters at prediction time.  ``mcmc_run_kwargs`` reaches the
+        sampler (``sampler="nuts"|"hmc"``, ``target_accept``, ``max_tree_depth``, ...)."""
         from . import infer
 
         if self.x is None:
             raise ValueError("fit() needs data: x and y are None")
         key, rng = state.get_rng_key()
         ld = infer.LogDensity(self.kernel, self.mean, self.x_transformed, self.y_transformed)
-        draws, info = infer.run_hmc(ld, self.num_warmup, self.hp_samples, self.num_chains, rng,
-                                    **self.mcmc_run_kwargs)
+        draws, info = infer.run(ld, self.num_warmup, self.hp_samples, self.num_chains, rng,
+                                chain_method=self.chain_method, **self.mcmc_run_kwargs)
         flat = draws.reshape(-1, draws.shape[-1])          # group_by_chain=False
         samples = ld.constrained(flat)
         for name, p in self.kernel._params.items():        # constants are not sample sites

@@ -53,7 +53,7 @@ class Mean(Prior):
         for k, p in self._params.items():
             if k in hp:
                 v = np.asarray(hp[k], float)
-                v = v[s] if v.shape[0] > 1 or v.ndim > 1 else v.reshape(-1)[0]
+                v = v.reshape(-1)[0] if v.size == 1 else v[s]
                 out[k] = float(v) if np.ndim(v) == 0 else np.asarray(v, float)
             elif p.is_constant:
                 out[k] = float(p.value)
@@ -67,7 +67,8 @@ class Mean(Prior):
         x = np.asarray(x, float)
         N = x.shape[0]
         if not any(k in hp for k in self._params):
-            return np.broadcast_to(np.asarray(self.__call__(x, **self._params_at(hp, 0)), float), (N,)).reshape(1, N).copy()
+            v = np.broadcast_to(np.asarray(self.__call__(x, **self._params_at(hp, 0)), float), (N,))
+            return v.reshape(1, N).copy()
         out = np.empty((S, N))
         for s in range(S):
             out[s] = np.broadcast_to(np.asarray(self.__call__(x, **self._params_at(hp, s)), float), (N,))
@@ -83,6 +84,7 @@ class Mean(Prior):
             return {k: np.asarray(an[k], float).reshape(N, -1) for k in names}
         out = {}
         for k in names:
+            scalar = np.ndim(params[k]) == 0
             v0 = np.atleast_1d(np.asarray(params[k], float))
             J = np.empty((N, v0.size))
             for q in range(v0.size):
@@ -90,9 +92,8 @@ class Mean(Prior):
                 hi, lo = v0.copy(), v0.copy()
                 hi[q] += h
                 lo[q] -= h
-                as_arg = (lambda a: float(a[0])) if np.ndim(params[k]) == 0 else (lambda a: a)
-                f1 = np.broadcast_to(self.__call__(x, **{**params, k: as_arg(hi)}), (N,))
-                f0 = np.broadcast_to(self.__call__(x, **{**params, k: as_arg(lo)}), (N,))
+                f1 = np.broadcast_to(self.__call__(x, **{**params, k: float(hi[0]) if scalar else hi}), (N,))
+                f0 = np.broadcast_to(self.__call__(x, **{**params, k: float(lo[0]) if scalar else lo}), (N,))
                 J[:, q] = (f1 - f0) / (2.0 * h)
             out[k] = J
         return out

@@ -14,7 +14,7 @@ from gpax_b200.acquisition import (EI, UCB, UE, ExpectedImprovement, Uncertainty
                                    UpperConfidenceBound)
 from gpax_b200.gp import ExactGP, GPSample, _affine_of
 from gpax_b200.kernels import MaternKernel, Parameter, PeriodicKernel, RBFKernel
-from gpax_b200.means import ConstantMean
+from gpax_b200.means import ConstantMean, Mean
 from gpax_b200.transforms import IdentityTransform, NormalizeTransform, ScaleTransform
 from oracle import gp_oracle as O  # checker only
 
@@ -164,9 +164,90 @@ def test_hmc_on_analytic_target():
     np.testing.assert_allclose(np.cov(flat.T), A, atol=0.25)
 
 
+def test_nuts_on_analytic_target():
+    """NUTS alone (no device): badly scaled 4-d Gaussian, 4 lock-step chains; the diagonal
+    mass-matrix adaptation has to find the scales (1, 0.1, 5, 0.01)."""
+    mu = np.array([1.0, -2.0, 0.5, 10.0])
+    sd = np.array([1.0, 0.1, 5.0, 0.01])
+
+    class Site:
+        plate, prior = 4, D.Normal(0.0, 1.0)
+
+        def unconstrain(self, t):
+            return t
+
+    class Target:
+        dim, sites, n_evals = 4, [Site()], 0
+
+        def __call__(self, u):
+            self.n_evals += 1
+            z = (u - mu) / sd
+            return -0.5 * np.sum(z * z, axis=1), -z / sd
+
+    out, info = infer.run_nuts(Target(), 400, 800, 4, np.random.default_rng(0))
+    flat = out.reshape(-1, 4)
+    assert info["sampler"] == "nuts" and np.all(info["divergences"] == 0)
+    assert np.all(info["accept"] > 0.6) and np.all(info["tree_depth"] <= 5)
+    np.testing.assert_allclose((flat.mean(0) - mu) / sd, 0.0, atol=0.15)
+    np.testing.assert_allclose(flat.std(0) / sd, 1.0, atol=0.12)
+    # sequential chains give the same shapes through the dispatcher
+    o2, i2 = infer.run(Target(), 60, 40, 2, np.random.default_rng(1), chain_method="sequential")
+    assert o2.shape == (2, 40, 4) and i2["accept"].shape == (2,)
+    wins = infer._adaptation_windows(1000)
+    assert wins[0] == (0, 74, False) and wins[-1] == (950, 999, False) and all(w[2] for w in wins[1:-1])
+    assert wins[1][0] == 75 and all(a[1] + 1 == b[0] for a, b in zip(wins, wins[1:]))
+
+
+class _Piecewise(Mean):
+    """examples/04_Structured_GP.ipynb cell 10, declared the way the notebook does (class-level
+    Parameter defaults)."""
+    m_t = Parameter(D.Uniform(0.5, 2.5))
+    m_beta1 = Parameter(D.LogNormal(0, 1))
+    m_beta2 = Parameter(D.LogNormal(0, 1))
+
+    def _mean_function(self, x, **params):
+        x = x.reshape(-1)
+        return np.piecewise(x, [x < params["m_t"], x >= params["m_t"]],
+                            [lambda v: v ** params["m_beta1"], lambda v: v ** params["m_beta2"]])
+
+
+def test_mean_with_learnable_parameters_host_side():
+    m = _Piecewise()
+    assert list(m._params) == ["m_t", "m_beta1", "m_beta2"] and m.learnable() == ["m_t", "m_beta1", "m_beta2"]
+    x = np.linspace(0.1, 3.0, 9)
+    hp = {"m_t": np.array([1.0, 2.0]), "m_beta1": np.array([2.0, 3.0]), "m_beta2": np.array([1.0, 0.5]),
+          "k_scale": np.ones(2)}
+    v = m.evaluate(x, hp, 2)
+    assert v.shape == (2, 9)
+    np.testing.assert_allclose(v[1], np.where(x < 2.0, x**3.0, x**0.5))
+    assert ConstantMean(2.0).evaluate(x, hp, 2).shape == (1, 9)
+    J = m.jacobian(x, m_t=1.0, m_beta1=2.0, m_beta2=1.5)
+    np.testing.assert_allclose(J["m_beta1"][:, 0], np.where(x < 1.0, x**2.0 * np.log(x), 0.0), rtol=1e-6, atol=1e-9)
+    assert J["m_t"].shape == (9, 1)
+    with pytest.raises(ValueError):
+        m.evaluate(x, {"m_t": np.ones(1), "k_scale": np.ones(1)}, 1)     # m_beta1 has no value
+
+
+def test_exactgp_signature_follows_reference():
+    """gpax/gp.py:114-131,506-510: field names, order and defaults."""
+    import inspect
+    sig = inspect.signature(ExactGP.__init__)
+    names = list(sig.parameters)[1:]
+    assert names == ["kernel", "x", "y", "y_std", "observation_noise", "hp_samples", "gp_samples",
+                     "input_transform", "output_transform", "metadata", "use_cholesky", "mean", "mcmc",
+                     "num_warmup", "num_chains", "chain_method", "mcmc_run_kwargs"]
+    d = {k: v.default for k, v in sig.parameters.items()}
+    assert d["chain_method"] == "sequential" and d["use_cholesky"] is False and d["mcmc"] is None
+    assert d["hp_samples"] == 100 and d["gp_samples"] == 10 and d["num_warmup"] == 2000 and d["num_chains"] == 1
+    gp = ExactGP(kernel=RBFKernel(), use_cholesky=True)
+    assert "solver" in gp.metadata and gp.mcmc is None and not gp._is_fit
+    with pytest.raises(ValueError):
+        ExactGP(kernel=RBFKernel(), chain_method="threads")
+
+
 def test_site_bijections():
     for prior, t in ((D.LogNormal(0, 1), 0.3), (D.Uniform(1.0, 3.0), 2.5), (D.Normal(0, 1), -0.7)):
-        s = infer._Site("k_x", Parameter(prior, 1))
+        s = infer._Site("k_x", Parameter(prior, 1), "kernel")
         u = s.unconstrain(np.array([t]))
         np.testing.assert_allclose(s.constrain(u), t, rtol=1e-14)
         lj, dlj, dt = s.log_jac(u, s.constrain(u))
@@ -267,7 +348,8 @@ def test_sample_shapes_and_draw_statistics(cuda):
 def test_fit_recovers_sinusoid(cuda):
     x, y = _sinusoid(28, seed=2)
     state.set_rng_key(1)
-    gp = ExactGP(kernel=RBFKernel(), x=x, y=y, hp_samples=60, num_warmup=150, num_chains=4)
+    gp = ExactGP(kernel=RBFKernel(), x=x, y=y, hp_samples=60, num_warmup=150, num_chains=4,
+                 chain_method="vectorized")
     gp.fit()
     assert gp._is_fit and "fit_key" in gp.metadata
     smp = gp.mcmc["samples"]
@@ -358,3 +440,87 @@ def test_monte_carlo_acquisition_q2(cuda):
     assert xb.shape == (2, 1) and np.isfinite(vb)
     e = EI(bounds=b, q=1, force_monte_carlo=True, fast=True)
     assert e(gp, xx[:, 0, :]).shape == (11,)
+
+
+# ---------------------------------------------------------------------------
+# GPU: learnable mean parameters (BASELINE config 5 shape) through the facade
+# ---------------------------------------------------------------------------
+class _Structured(Mean):
+    """synthetic.structured_mean as a user Mean with m_* parameters (notebook 04 cell 10, d = 3)."""
+    m_t = Parameter(D.Uniform(0.5, 2.5))
+    m_beta1 = Parameter(D.LogNormal(0, 1))
+    m_beta2 = Parameter(D.LogNormal(0, 1))
+
+    def _mean_function(self, x, **p):
+        from gpax_b200.synthetic import structured_mean
+        return structured_mean(x, p["m_t"], p["m_beta1"], p["m_beta2"])
+
+
+@pytest.mark.gpu
+def test_c5_golden_through_facade_with_learnable_mean(cuda):
+    """The C5 golden (Periodic + piecewise power-law mean, identity transforms) through
+    ``ExactGP.sample`` / ``predict`` with the posterior samples injected as ``mcmc`` output:
+    per-sample mean / sd against the golden at 1e-10 (normwise), pooled moments against the
+    oracle's mixture."""
+    import os
+    z = np.load(os.path.join(os.path.dirname(__file__), "golden", "c5_small.npz"), allow_pickle=False)
+    hp = {k[3:]: z[k] for k in z.files if k.startswith("hp_")}
+    samples = {k: v for k, v in hp.items() if k != "k_jitter"}
+    gp = ExactGP(kernel=PeriodicKernel(), mean=_Structured(), x=z["x"], y=z["y"], input_transform=None,
+                 output_transform=None, hp_samples=len(hp["k_scale"]), mcmc={"samples": samples})
+    assert gp._is_fit
+    np.testing.assert_allclose(gp._mean_values(z["x"], hp), z["m_train"], rtol=1e-14)
+    s = gp.sample(z["x_new"], draw=False)
+    rel = lambda a, b: float(np.max(np.abs(a - b)) / np.max(np.abs(b)))
+    assert rel(s.mu_per_hp, z["mu"]) < 1e-10
+    assert rel(s.sd_per_hp**2, z["var"]) < 1e-10
+    mu, sd = gp.predict(z["x_new"])
+    np.testing.assert_allclose(mu, z["mbar"], rtol=1e-10, atol=1e-12)
+    np.testing.assert_allclose(sd, np.sqrt(z["vbar"]), rtol=1e-9)
+    # fast=True: median of every parameter (mean parameters included), S = 1
+    mu_f, sd_f = gp.predict(z["x_new"], fast=True)
+    assert mu_f.shape == mu.shape and np.all(np.isfinite(sd_f))
+
+
+@pytest.mark.gpu
+def test_log_density_gradient_with_mean_parameters(cuda):
+    rng = np.random.default_rng(3)
+    x = rng.uniform(0.2, 3.0, (20, 3))
+    from gpax_b200.synthetic import structured_mean
+    y = structured_mean(x, 1.7, 2.0, 1.2) + 0.05 * rng.normal(size=20)
+    gp = ExactGP(kernel=RBFKernel(), mean=_Structured(), x=x, y=y, input_transform=None, output_transform=None)
+    ld = infer.LogDensity(gp.kernel, gp.mean, gp.x_transformed, gp.y_transformed)
+    assert ld.dim == 6 and [s.name for s in ld.mean_sites] == ["m_t", "m_beta1", "m_beta2"]
+    u = rng.normal(0.0, 0.3, (3, ld.dim))
+    lp, g = ld(u)
+    assert np.all(np.isfinite(lp))
+    h = 1e-5
+    for j in range(ld.dim):
+        e = np.zeros_like(u)
+        e[:, j] = h
+        fd = (ld(u + e)[0] - ld(u - e)[0]) / (2 * h)
+        # m_t moves a kink across data points: compare where the density is smooth in it
+        np.testing.assert_allclose(g[:, j], fd, rtol=2e-4, atol=2e-4)
+
+
+@pytest.mark.gpu
+def test_fit_structured_gp_notebook_shape(cuda):
+    """examples/04_Structured_GP.ipynb cells 4, 10, 11: 15 noisy points of a piecewise power law,
+    MaternKernel + learnable piecewise mean, no transforms; fit() then predict()."""
+    np.random.seed(1)
+    x = np.random.uniform(0, 3, 15)
+    truth = lambda v: np.where(v < 1.7, v**4.5, v**2.5)
+    y = truth(x) + np.random.normal(0.0, 0.1, 15)
+    state.set_rng_key(3)
+    gp = ExactGP(kernel=MaternKernel(), mean=_Piecewise(), input_transform=None, output_transform=None,
+                 x=x.reshape(-1, 1), y=y, hp_samples=60, num_warmup=120, num_chains=4,
+                 chain_method="vectorized", mcmc_run_kwargs={"max_tree_depth": 6})
+    gp.fit()
+    smp = gp.mcmc["samples"]
+    assert {"m_t", "m_beta1", "m_beta2", "k_scale", "k_length", "k_noise"} <= set(smp)
+    assert smp["m_t"].shape == (240,) and np.all((smp["m_t"] > 0.5) & (smp["m_t"] < 2.5))
+    assert gp.mcmc["sampler"] == "nuts"
+    xg = np.linspace(0.05, 3, 40).reshape(-1, 1)
+    mu, sd = gp.predict(xg)
+    assert mu.shape == (40,) and np.all(np.isfinite(mu)) and np.all(np.isfinite(sd))
+    assert np.median(np.abs(mu - truth(xg[:, 0]))) < 1.0
