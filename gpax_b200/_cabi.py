@@ -16,6 +16,7 @@ RBF, MATERN52, PERIODIC = 0, 1, 2
 ACQ_EI, ACQ_UCB, ACQ_UE, ACQ_MEAN = 0, 1, 2, 3
 FULL, LOWER = 0, 1
 NB = 128
+STATIC_SCRATCH_BYTES = 8 << 20      # GPX_STATIC_SCRATCH_BYTES (gpx_predict_static)
 MAX_D = 8
 KIND_BY_NAME = {"rbf": RBF, "matern52": MATERN52, "periodic": PERIODIC}
 
@@ -60,6 +61,8 @@ SIGNATURES = {
     "gpx_predict_ws_bytes": (_sz, [_i64, _i64, _i32]),
     "gpx_predict": (C.c_int, [_kp, _i64, _i64, _i64, _ptr, _ptr, _ptr, _i64, _ptr, _ptr, _dbl,
                               _ptr, _ptr, _ptr, _ptr, _ptr]),
+    "gpx_predict_static": (C.c_int, [_kp, _i64, _i64, _i64, _ptr, _ptr, _ptr, _i64, _ptr, _ptr, _dbl,
+                                     _ptr, _ptr, _ptr, _ptr]),
     "gpx_acq_parts": (_i64, [_i64]),
     "gpx_acq_reduce": (C.c_int, [_i64, _i64, _ptr, _ptr, _i32, _dbl, _dbl, _dbl, _dbl, _dbl,
                                  _i64, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr]),
@@ -76,7 +79,7 @@ for _name, (_res, _args) in SIGNATURES.items():
     _fn.restype = _res
     _fn.argtypes = _args
 
-ABI_VERSION = 4
+ABI_VERSION = 5
 if lib.gpx_abi_version() != ABI_VERSION:
     raise ImportError("libgpax_b200.so ABI version mismatch")
 

@@ -33,6 +33,7 @@
 // staged once per call into a small workspace xs[S][n][d+2] by a prep kernel.
 #include <cuda.h>
 #include <cstdlib>
+#include <mutex>
 #include "predict_small.cuh"
 #include "predict_tiny.cuh"
 
@@ -910,4 +911,64 @@ extern "C" int gpx_predict_acq(const gpx_kernel_params *kp, int64_t S, int64_t n
     if (best_val || best_idx)
         return gpx_argmax_finalize(gpx_acq_parts(M), part_val, part_idx, best_val, best_idx, stream);
     return 0;
+}
+
+// ---------------------------------------------------------------------------
+// gpx_predict_static: gpx_predict for callers that cannot allocate (CUDA graph capture, tight
+// serving loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+// The scratch gpx_predict takes from the caller (the staged
+// per-sample training rows, gpx_predict_ws_bytes) lives in a file-scope device array of
+// GPX_STATIC_SCRATCH_BYTES that every GPU loading this library holds until exit.
+//  * In host code `g_static_scratch` is only a host-side stand-in for the symbol, NOT a device
+//    address: the device address is resolved once per device, with that device current, by
+//    cudaGetSymbolAddress and cached; that pointer is what the kernels receive.
+//  * Nothing in the array has to start at zero: predict_prep_kernel rewrites every row (padding
+//    rows included) the main kernel later reads, so the previous call's contents are never seen.
+//  * Every call on a device shares the one array: calls that overlap on the GPU (different
+//    streams, or graph branches without a dependency) race on it.  Serialise them.
+//  * No cudaMalloc / cudaFree / allocating library routine is called here or below.
+// ---------------------------------------------------------------------------
+static __device__ __align__(256) double g_static_scratch[GPX_STATIC_SCRATCH_BYTES / sizeof(double)];
+
+// device address of g_static_scratch on the calling thread's current device (0 on success)
+static int static_scratch_ptr(double **out) {
+    static double *ptrs[64] = {};
+    static std::mutex mu;
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return (int)e;
+    if (dev < 0 || dev >= 64) return (int)cudaErrorInvalidDevice;
+    std::lock_guard<std::mutex> lock(mu);
+    if (!ptrs[dev]) {
+        void *p = nullptr;
+        e = cudaGetSymbolAddress(&p, g_static_scratch);
+        if (e != cudaSuccess || !p) {
+            gpx::set_error("gpx_predict_static: cudaGetSymbolAddress failed: %d (%s)", (int)e,
+                           cudaGetErrorString(e));
+            return e != cudaSuccess ? (int)e : (int)cudaErrorInvalidSymbol;
+        }
+        ptrs[dev] = (double *)p;
+    }
+    *out = ptrs[dev];
+    return 0;
+}
+
+extern "C" int gpx_predict_static(const gpx_kernel_params *kp, int64_t S, int64_t n, int64_t M,
+                                  const double *x, const double *xnew, const double *W, int64_t ldw,
+                                  const double *alpha, const double *m_new, double m_const,
+                                  const double *diag_add, double *mu, double *var, void *stream) {
+    using namespace gpx;
+    if (int rc = predict_check_args(kp, S, n, M, x, xnew, W, ldw, alpha, diag_add)) return rc;
+    const size_t need = gpx_predict_ws_bytes(S, n, kp->d);
+    if (need > (size_t)GPX_STATIC_SCRATCH_BYTES) {
+        set_error("gpx_predict_static: S=%lld, n=%lld, d=%d needs %zu bytes of scratch, the built-in array "
+                  "holds GPX_STATIC_SCRATCH_BYTES = %zu; use gpx_predict with a caller workspace",
+                  (long long)S, (long long)n, (int)kp->d, need, (size_t)GPX_STATIC_SCRATCH_BYTES);
+        return -3;
+    }
+    if (S == 0 || M == 0) return 0;
+    double *scratch = nullptr;
+    if (int rc = static_scratch_ptr(&scratch)) return rc;
+    return predict_core(kp, S, n, M, x, xnew, W, ldw, alpha, m_new, m_const, diag_add, mu, var, M, M,
+                        true, scratch, (cudaStream_t)stream);
 }

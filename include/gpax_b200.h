@@ -42,7 +42,7 @@
 extern "C" {
 #endif
 
-#define GPX_ABI_VERSION 4
+#define GPX_ABI_VERSION 5
 
 /* covariance families: gpax/kernels.py:110 (RBF), :129 (Matern nu=5/2), :150 (Periodic) */
 enum { GPX_RBF = 0, GPX_MATERN52 = 1, GPX_PERIODIC = 2 };
@@ -158,6 +158,25 @@ int gpx_predict(const gpx_kernel_params *kp, int64_t S, int64_t n, int64_t M,
                 const double *W, int64_t ldw, const double *alpha,
                 const double *m_new, double m_const, const double *diag_add,
                 double *mu, double *var, void *ws, void *stream);
+
+/* gpx_predict_static: gpx_predict WITHOUT a caller workspace, for callers that cannot
+ * allocate (code under CUDA graph capture, tight serving loops, harnesses that forbid
+ * cudaMalloc).  It has NO counterpart in the reference and replaces no call site there.
+ * Arguments and results are those of
+ * gpx_predict minus `ws`; the scratch (gpx_predict_ws_bytes(S, n, d) bytes) is a static
+ * device array of GPX_STATIC_SCRATCH_BYTES built into the library -- every GPU that loads
+ * the library holds it until exit.  Larger problems are rejected with -3 and a diagnostic
+ * (e.g. d = 2, n = 2048: S <= 85 fits).  The call allocates nothing (no cudaMalloc /
+ * cudaFree / allocating library routine); the array's device address is resolved once per
+ * device on first use.  All calls on a device SHARE the array, which keeps the previous
+ * call's contents (every element read is rewritten first, so nothing needs clearing):
+ * calls that overlap on the GPU race -- serialise them on one stream. */
+#define GPX_STATIC_SCRATCH_BYTES (8u << 20)
+int gpx_predict_static(const gpx_kernel_params *kp, int64_t S, int64_t n, int64_t M,
+                       const double *x, const double *xnew,
+                       const double *W, int64_t ldw, const double *alpha,
+                       const double *m_new, double m_const, const double *diag_add,
+                       double *mu, double *var, void *stream);
 
 /* ---------------------------------------------------------------------------
  * gpx_acq_reduce: mixture moments over S (fixed order s = 0..S-1), reverse
