@@ -114,7 +114,14 @@ class AcquisitionFunction:
         return samples.reshape(n_samples, self.q, -1)
 
     def _optimize_halton(self, model, n_samples):
-        """gpax/acquisition.py:166-216: best of ``n_samples`` Halton points."""
+        """gpax/acquisition.py:166-216: best of ``n_samples`` Halton points.
+
+        Contract difference, flagged: the reference stacks the per-chunk values with
+        ``jnp.array(vals)`` (gpax/acquisition.py:211), which only works when
+        ``n_samples % batch_threshold == 0`` (ragged chunks raise there).  Here the analytic
+        path evaluates all candidates in one fused device sweep, so any ``n_samples`` is
+        accepted; for multiples of ``batch_threshold`` the result is the reference's (same
+        Halton points, same first-maximum rule)."""
         samples = self._halton(n_samples)
         if self.force_monte_carlo or self.q > 1:
             vals = np.concatenate([
@@ -138,8 +145,12 @@ class UpperConfidenceBound(AcquisitionFunction):
     """``mu + sqrt(beta + 1e-12) * sd``; ``beta == inf`` -> ``sd``; ``beta == 0`` ->
     ``mu`` (gpax/acquisition.py:244-275)."""
 
-    def __init__(self, bounds, beta=10.0, **kwargs):
-        super().__init__(bounds, **kwargs)
+    def __init__(self, bounds, q=1, penalty_function=None, penalty_strength=0.0,
+                 batch_threshold=100, force_monte_carlo=False, fast=True, beta=10.0):
+        # attrs field order of the reference: the base-class fields, then beta
+        # (gpax/acquisition.py:44-54,253)
+        super().__init__(bounds, q, penalty_function, penalty_strength, batch_threshold,
+                         force_monte_carlo, fast)
         if not isinstance(beta, (int, float)) or isinstance(beta, bool):
             raise TypeError("beta must be an int or float")
         if beta < 0.0:
@@ -191,8 +202,10 @@ class ExpectedImprovement(AcquisitionFunction):
 class UncertaintyExploration(UpperConfidenceBound):
     """Pure exploration: UCB with ``beta = inf``."""
 
-    def __init__(self, bounds, **kwargs):
-        super().__init__(bounds, beta=float("inf"), **kwargs)
+    def __init__(self, bounds, q=1, penalty_function=None, penalty_strength=0.0,
+                 batch_threshold=100, force_monte_carlo=False, fast=True):
+        super().__init__(bounds, q, penalty_function, penalty_strength, batch_threshold,
+                         force_monte_carlo, fast, beta=float("inf"))
 
 
 EI = ExpectedImprovement

@@ -25,3 +25,14 @@ done
 for p in "${pids[@]}"; do wait "$p"; done
 "$NVCC" -shared -o "$out/libgpax_b200.so" "$here"/obj/*.o -lcudart
 echo "built $out/libgpax_b200.so"
+
+# jax.ffi handlers (xla_ffi_shim.cc): only where JAX -- and with it the XLA FFI headers -- exists.
+# JAX is absent from this image and from the GPU box, so this rule is normally skipped.
+if ffi_inc="$(python -c 'import jax; print(jax.ffi.include_dir())' 2>/dev/null)" && [ -d "$ffi_inc" ]; then
+  "${CXX:-g++}" -O2 -std=c++17 -fPIC -shared -I"$ffi_inc" -I/usr/local/cuda/include \
+      "$here/xla_ffi_shim.cc" -o "$out/libgpax_b200_xla.so" \
+      -L"$out" -lgpax_b200 -Wl,-rpath,'$ORIGIN' -L/usr/local/cuda/lib64 -lcudart
+  echo "built $out/libgpax_b200_xla.so (jax.ffi handlers)"
+else
+  echo "jax not importable: skipped xla_ffi_shim.cc (compile-gated, see INTEGRATION.md section 3)"
+fi

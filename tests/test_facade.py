@@ -524,3 +524,16 @@ def test_fit_structured_gp_notebook_shape(cuda):
     mu, sd = gp.predict(xg)
     assert mu.shape == (40,) and np.all(np.isfinite(mu)) and np.all(np.isfinite(sd))
     assert np.median(np.abs(mu - truth(xg[:, 0]))) < 1.0
+
+
+def test_acquisition_signatures_follow_reference():
+    """attrs field order of gpax/acquisition.py:44-54,253: base fields first, beta last."""
+    import inspect
+    base = ["bounds", "q", "penalty_function", "penalty_strength", "batch_threshold", "force_monte_carlo", "fast"]
+    assert list(inspect.signature(ExpectedImprovement.__init__).parameters)[1:] == base
+    assert list(inspect.signature(UpperConfidenceBound.__init__).parameters)[1:] == base + ["beta"]
+    b = np.array([[0.0], [1.0]])
+    a = UpperConfidenceBound(b, 2, None, 0.0, 50, False, False, 3.0)      # all positional, reference order
+    assert (a.q, a.batch_threshold, a.fast, a.beta) == (2, 50, False, 3.0)
+    d = inspect.signature(UpperConfidenceBound.__init__).parameters
+    assert d["beta"].default == 10.0 and d["fast"].default is True and d["batch_threshold"].default == 100

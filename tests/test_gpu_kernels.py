@@ -522,6 +522,29 @@ def test_c2_ill_conditioned_samples_adjudicated(cuda):
         assert v_dev < max(1e-10, 4 * v_lap), (idx[q], v_dev, v_lap)
 
 
+@pytest.mark.parametrize("name", ["c1_small", "c2_small"])
+def test_device_vs_default_inv_branch(cuda, name):
+    """GPU against the reference's DEFAULT branch (use_cholesky=False, gpax/gp.py:303-310) at the
+    tolerance documented in tests/test_oracle.py::test_default_inv_branch_gap: mean within
+    50 * cond(K) * eps, diag(cov) within 1000 * cond(K) * eps (the inv branch's own error)."""
+    import torch
+    from gpax_b200 import engine as E
+    z = np.load(_os.path.join(_GOLD, name + ".npz"), allow_pickle=False)
+    hp = {k[3:]: z[k] for k in z.files if k.startswith("hp_")}
+    kind = str(z["kind"])
+    post = E.Posterior(kind, z["x"], z["y"], hp, device=cuda)
+    mu, var = post.predict(z["x_new"])
+    torch.cuda.synchronize()
+    mu_i, var_i = O.predict_batched(kind, z["x"], z["y"], z["x_new"], hp, use_cholesky=False)
+    eps = np.finfo(float).eps
+    for s in range(len(hp["k_scale"])):
+        K = O.gram(kind, z["x"], z["x"], hp["k_scale"][s], hp["k_length"][s], None, hp["k_noise"][s],
+                   hp["k_jitter"][s])
+        cond = np.linalg.cond(K)
+        assert _rel(mu[s].cpu().numpy(), mu_i[s]) < 50 * cond * eps
+        assert _rel(var[s].cpu().numpy(), var_i[s]) < 1000 * cond * eps
+
+
 def test_c5_full_size_vs_oracle(cuda):
     """BASELINE config C5 at its own size (Periodic + piecewise power-law mean, d=3, n=1024,
     M=10^4, per-sample m_train / m_new)."""

@@ -280,3 +280,55 @@ def test_extended_precision_adjudicator_matches_mpmath(name):
         e_m = _rel(np.asarray(m, float), z["mp_mu"][s])
         e_v = _rel(np.asarray(v, float), z["mp_var"][s])
         assert e_m < 1e-14 and e_v < 1e-13, (s, e_m, e_v)
+
+
+def _inv_gap(name, S_max=4):
+    """normwise gaps between the reference's two branches (gpax/gp.py:295-301 vs :303-310) and of
+    each to the extended-precision answer, with cond(K), per sample."""
+    from oracle import ld_oracle as LDO
+    z, hp = _load(name)
+    kind = str(z["kind"])
+    xn = z["x_new"][:60]
+    rows = []
+    for s in range(min(S_max, len(hp["k_scale"]))):
+        mt = z["m_train"][s] if "m_train" in z.files else np.ones(len(z["x"]))
+        mn = z["m_new"][s][:60] if "m_new" in z.files else np.ones(len(xn))
+        per = hp["k_period"][s] if "k_period" in hp else None
+        args = (kind, z["x"], z["y"], xn, mt, mn, hp["k_scale"][s], hp["k_length"][s], hp["k_noise"][s],
+                hp["k_jitter"][s], per)
+        m_c, c_c = O.mean_and_covariance(*args, use_cholesky=True)
+        m_i, c_i = O.mean_and_covariance(*args, use_cholesky=False)
+        K = O.gram(kind, z["x"], z["x"], hp["k_scale"][s], hp["k_length"][s], per, hp["k_noise"][s], hp["k_jitter"][s])
+        row = {"cond": float(np.linalg.cond(K)), "mu_gap": _rel(m_i, m_c), "var_gap": _rel(np.diag(c_i), np.diag(c_c))}
+        if LDO.has_extended_precision():
+            m_x, v_x, _ = LDO.predict(*args)
+            row.update(mu_chol=_rel(m_c, np.asarray(m_x, float)), mu_inv=_rel(m_i, np.asarray(m_x, float)),
+                       var_chol=_rel(np.diag(c_c), np.asarray(v_x, float)),
+                       var_inv=_rel(np.diag(c_i), np.asarray(v_x, float)))
+        rows.append(row)
+    return rows
+
+
+@pytest.mark.parametrize("name", ["c1_small", "c2_small"])
+def test_default_inv_branch_gap(name):
+    """N4 (parity statement for the reference's DEFAULT branch, ``use_cholesky=False``:
+    ``jnp.linalg.inv`` then two GEMMs, gpax/gp.py:303-310).  The device path implements the
+    Cholesky branch; the two are the same mathematics and differ by rounding amplified by
+    cond(K).  Measured here (c1_small / c2_small, cond(K) 3.6e3 .. 2.5e5):
+      * mean: gap <= 2.1e-11, i.e. <= 50 * cond * eps, and < 1e-10 for cond <= 1e5;
+      * diag(cov): gap up to 1.9e-8 (<= 1000 * cond * eps) -- and that gap is the inv branch's
+        OWN error: against the extended-precision answer the Cholesky branch is at <= 2e-12
+        where the inv branch is at 1.9e-8 (explicit inverse, then cancellation in
+        k** - k* K^-1 k*^T).
+    So 1e-10 parity is claimed against the use_cholesky=True branch; against the default branch
+    the documented tolerance is the one asserted below, and superseding
+    the default branch never costs accuracy."""
+    eps = np.finfo(float).eps
+    for r in _inv_gap(name, 8):
+        assert r["mu_gap"] < 50 * r["cond"] * eps, r
+        assert r["var_gap"] < 1000 * r["cond"] * eps, r
+        if r["cond"] <= 1e5:
+            assert r["mu_gap"] < 1e-10, r
+        if "mu_chol" in r:
+            assert r["mu_chol"] < max(1e-13, 4 * r["mu_inv"]), r
+            assert r["var_chol"] < max(1e-13, 4 * r["var_inv"]), r
