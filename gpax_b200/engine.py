@@ -247,6 +247,24 @@ def predict_acq(hpd: HyperParams, x, x_new, W, alpha, diag_add, acq, beta=10.0, 
     return o_mu, o_sd, o_acq, bv, bi
 
 
+def draw(hpd: HyperParams, x, x_new, W, mu, G, key, diag_noise=None, partitionable=False):
+    """``gpx_draw``: joint draws ``y [S, G, M]`` (gpax/gp.py:335-337).  ``x`` / ``W`` are None for
+    the unconditioned prior; ``key`` is the integer of ``state.get_rng_key`` (JAX key (0, key))."""
+    S, M = mu.shape
+    dev = mu.device
+    n = 0 if x is None else x.shape[0]
+    ws = torch.empty(max(1, lib.gpx_draw_ws_bytes(S, n, M, G) // 8), dtype=F64, device=dev)
+    y = torch.empty((S, G, M), dtype=F64, device=dev)
+    info = torch.zeros(S, dtype=torch.int32, device=dev)
+    key = int(key)
+    mu = mu.contiguous()          # held in a local: _ptr keeps no reference to a temporary
+    check(lib.gpx_draw(C.byref(hpd.kp), S, n, M, G, _ptr(x), _ptr(x_new), _ptr(W),
+                       0 if W is None else W.shape[2], _ptr(mu), _ptr(diag_noise),
+                       _ptr(hpd.jitter), (key >> 32) & 0xFFFFFFFF, key & 0xFFFFFFFF,
+                       1 if partitionable else 0, _ptr(y), _ptr(info), _ptr(ws), _stream()), "gpx_draw")
+    return y, info
+
+
 def argmax_finalize(pv, pi):
     dev = pv.device
     bv = torch.empty(1, dtype=F64, device=dev)

@@ -266,11 +266,9 @@ class GaussianProcess:
         return mu, var, post
 
     def _draw(self, rng_seed, x_new_t, hp, mu, post):
-        """Joint draws ``y [S, G, M]`` from ``N(mu_s, cov_s)`` (gpax/gp.py:332-338).
-        Row N1: covariance assembled with library GEMMs on the device, factorised by gpx_potrf_batched."""
-        import torch
-
-        from . import _cabi
+        """Joint draws ``y [S, G, M]`` from ``N(mu_s, cov_s)`` (gpax/gp.py:332-338) by ``gpx_draw``:
+        covariance, its Cholesky factor and JAX-compatible threefry normals all on the device.
+        ``state.threefry_partitionable`` selects JAX's counter layout (see ``gpx_random_normal``)."""
         from . import engine as E
 
         S, M = mu.shape
@@ -279,34 +277,19 @@ class GaussianProcess:
             raise ValueError(f"joint draws need {S}x{M}x{M} covariances; lower M or hp_samples, "
                              "or call sample(..., draw=False) / predict()")
         dev = mu.device
-        gen = torch.Generator(device=dev).manual_seed(int(rng_seed))
         xn = E._dev(np.asarray(x_new_t, float).reshape(M, -1), dev)
-        y = torch.empty((S, G, M), dtype=torch.float64, device=dev)
+        y = None
         chunk = max(1, _MAX_DRAW_ELEMS // max(1, M * max(M, 0 if post is None else post.n)))
-        for s0 in range(0, S, chunk):
-            sl = slice(s0, min(S, s0 + chunk))
-            sub = {k: np.asarray(v)[sl] for k, v in hp.items()}
-            if not self.observation_noise:
-                sub["k_noise"] = np.zeros(len(sub["k_scale"]))
-            hpd = E.HyperParams(self.kernel.kind, xn.shape[1], sub, dev)
-            cov = E.gram(hpd, xn, xn, add_diag=True)[:, :, :M]
-            if post is not None:
-                kx = E.gram(hpd, post.x, xn)[:, :, :M]                 # [s, n, M]
-                W = torch.tril(post.W[sl, :, : post.n])
-                V = torch.bmm(W, kx)
-                cov = cov - torch.bmm(V.transpose(1, 2), V)
-            # factor of the posterior covariance with the library's own batched blocked Cholesky
-            # (gpx_potrf_batched, lower triangle in place; leading dimension must be even)
-            ldc = M + (M & 1)
-            fac = torch.zeros((cov.shape[0], M, ldc), dtype=torch.float64, device=dev)
-            fac[:, :, :M] = cov
-            _, info = E.potrf(fac, M)
-            if int(info.abs().max()) != 0:
-                raise ValueError("posterior covariance at x_new is not positive definite "
-                                 "(add observation noise or jitter, or use fewer / more distinct points)")
-            Lc = torch.tril(fac[:, :, :M])
-            z = torch.randn((Lc.shape[0], M, G), dtype=torch.float64, device=dev, generator=gen)
-            y[sl] = mu[sl, None, :] + torch.bmm(Lc, z).transpose(1, 2)
+        if chunk < S:
+            raise ValueError(f"joint draws of {S} samples at M={M} exceed the draw workspace; lower M "
+                             "or hp_samples, or call sample(..., draw=False) / predict()")
+        hpd = post.hpd if post is not None else E.HyperParams(self.kernel.kind, xn.shape[1], hp, dev)
+        y, info = E.draw(hpd, None if post is None else post.x, xn, None if post is None else post.W,
+                         mu, G, rng_seed, diag_noise=hpd.noise if self.observation_noise else None,
+                         partitionable=state.threefry_partitionable)
+        if int(info.abs().max()) != 0:
+            raise ValueError("posterior covariance at x_new is not positive definite "
+                             "(add observation noise or jitter, or use fewer / more distinct points)")
         return y
 
     # -- public API ----------------------------------------------------------

@@ -17,6 +17,9 @@ _VERBOSITY = {"silent": 0, "normal": 1, "debug": 2}
 
 rng_key = 0
 verbose = 1
+#: counter layout of the threefry draws (``gpx_random_normal``): False = jax_threefry_partitionable
+#: off (default of the reference's minimum jax 0.4.31), True = the default from jax 0.5.0
+threefry_partitionable = False
 
 
 def set_rng_key(key: int) -> None:

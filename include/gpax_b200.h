@@ -42,7 +42,7 @@
 extern "C" {
 #endif
 
-#define GPX_ABI_VERSION 5
+#define GPX_ABI_VERSION 6
 
 /* covariance families: gpax/kernels.py:110 (RBF), :129 (Matern nu=5/2), :150 (Periodic) */
 enum { GPX_RBF = 0, GPX_MATERN52 = 1, GPX_PERIODIC = 2 };
@@ -235,6 +235,40 @@ int gpx_predict_acq(const gpx_kernel_params *kp, int64_t S, int64_t n, int64_t M
                     double *out_mu, double *out_sd, double *out_acq,
                     double *part_val, int64_t *part_idx,
                     double *best_val, int64_t *best_idx, void *ws, void *stream);
+
+/* ---------------------------------------------------------------------------
+ * Joint posterior draws (row N1): y[S, G, M] ~ N(mu_s, cov_s), replacing
+ * dist.MultivariateNormal(mean, cov).sample(key, (G,)) of gpax/gp.py:335-337 with
+ * keys = jax.random.split(rng_key, S) (gpax/gp.py:389) and rng_key = jax.random.key(int)
+ * = (0, int) (gpax/state.py:117-126).
+ *
+ * JAX's threefry PRNG is a third-party algorithm (jax>=0.4.31, pyproject.toml:25; not under
+ * /root/reference); it is restated from its published form and pinned by known-answer vectors:
+ *   gpx_threefry2x32  : the raw block function on n counter pairs (uint32 device arrays);
+ *   gpx_random_split  : jax.random.split(key, num) -> keys[num, 2];
+ *   gpx_random_normal : out[s][j * ldg + g] = element (g, j) of jax.random.normal(keys[s], (G, M))
+ *                       (float64: sqrt(2) * erfinv(uniform(nextafter(-1, 0), 1)));
+ *   partitionable = 0 : jax_threefry_partitionable=False counter layout (default of jax 0.4.x),
+ *   partitionable = 1 : the layout that became the default in jax 0.5.0.
+ *
+ * gpx_draw: cov_s = k(x*, x*) + diag - V^T V with V = W_s k(x, x*) (DMMA GEMMs; pass n = 0 for
+ * the unconditioned prior, gpax/gp.py:212-245), its Cholesky factor (gpx_potrf_batched; info[S]
+ * nullable), eps from the keys above, y[s, g, :] = mu[s, :] + L_s eps[g, :].
+ *   mu [S, M]; diag_noise [S] or NULL (k_noise if observation_noise, gpax/gp.py:283-287);
+ *   jitter [S]; y [S, G, M] out; ws: gpx_draw_ws_bytes(S, n, M, G) bytes (holds the [M, M]
+ *   covariances: meant for modest M). */
+int gpx_threefry2x32(int64_t n, uint32_t key0, uint32_t key1, const uint32_t *ctr0, const uint32_t *ctr1,
+                     uint32_t *out0, uint32_t *out1, void *stream);
+int gpx_random_split(uint32_t key0, uint32_t key1, int64_t num, int32_t partitionable,
+                     uint32_t *keys, void *stream);
+int gpx_random_normal(const uint32_t *keys, int64_t S, int64_t G, int64_t M, int32_t partitionable,
+                      double *out, int64_t ldg, void *stream);
+size_t gpx_draw_ws_bytes(int64_t S, int64_t n, int64_t M, int64_t G);
+int gpx_draw(const gpx_kernel_params *kp, int64_t S, int64_t n, int64_t M, int64_t G,
+             const double *x, const double *xnew, const double *W, int64_t ldw,
+             const double *mu, const double *diag_noise, const double *jitter,
+             uint32_t key0, uint32_t key1, int32_t partitionable,
+             double *y, int32_t *info, void *ws, void *stream);
 
 #ifdef __cplusplus
 }

@@ -332,3 +332,24 @@ def test_default_inv_branch_gap(name):
         if "mu_chol" in r:
             assert r["mu_chol"] < max(1e-13, 4 * r["mu_inv"]), r
             assert r["var_chol"] < max(1e-13, 4 * r["var_inv"]), r
+
+
+def test_threefry_known_answers_and_layouts():
+    """Threefry-2x32-20 against the Random123 known-answer vectors (the ones JAX's own tests
+    assert), and the structural properties of the restated split / normal."""
+    from oracle import jax_prng as R
+    for key, ctr, out in R.KAT:
+        a, b = R.threefry2x32(key, [ctr[0]], [ctr[1]])
+        assert (int(a[0]), int(b[0])) == out
+    k = R.key(1948878966)
+    assert (int(k[0]), int(k[1])) == (0, 1948878966)
+    for part in (False, True):
+        ks = R.split(k, 5, part)
+        assert ks.shape == (5, 2) and ks.dtype == np.uint32 and len({tuple(r) for r in ks.tolist()}) == 5
+        z = R.normal(ks[0], (4000, 8), part)
+        assert abs(z.mean()) < 0.02 and abs(z.std() - 1.0) < 0.02 and np.all(np.isfinite(z))
+        np.testing.assert_array_equal(z, R.normal(ks[0], (4000, 8), part))          # pure function of the key
+        assert not np.array_equal(z, R.normal(ks[1], (4000, 8), part))
+    # original layout: the first element of split's flat output is block 0's first word
+    a, b = R.threefry2x32(k, [0], [5])
+    assert int(R.split(k, 5, False)[0, 0]) == int(a[0]) and int(R.split(k, 5, False).reshape(-1)[5]) == int(b[0])
