@@ -72,6 +72,7 @@ SIGNATURES = {
     "gpx_predict_acq": (C.c_int, [_kp, _i64, _i64, _i64, _ptr, _ptr, _ptr, _i64, _ptr, _ptr, _dbl,
                                   _ptr, _i32, _dbl, _dbl, _dbl, _dbl, _dbl, _i64, _i64, _ptr, _ptr,
                                   _ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr]),
+    "gpx_halton": (C.c_int, [_i64, _i32, _i64, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr]),
     "gpx_threefry2x32": (C.c_int, [_i64, C.c_uint32, C.c_uint32, _ptr, _ptr, _ptr, _ptr, _ptr]),
     "gpx_random_split": (C.c_int, [C.c_uint32, C.c_uint32, _i64, _i32, _ptr, _ptr]),
     "gpx_random_normal": (C.c_int, [_ptr, _i64, _i64, _i64, _i32, _ptr, _i64, _ptr]),
@@ -85,7 +86,7 @@ for _name, (_res, _args) in SIGNATURES.items():
     _fn.restype = _res
     _fn.argtypes = _args
 
-ABI_VERSION = 6
+ABI_VERSION = 7
 if lib.gpx_abi_version() != ABI_VERSION:
     raise ImportError("libgpax_b200.so ABI version mismatch")
 

@@ -113,6 +113,41 @@ class AcquisitionFunction:
         samples = qmc.scale(samples, l_bounds, u_bounds)
         return samples.reshape(n_samples, self.q, -1)
 
+    def _bounds_tiled(self):
+        l_bounds = np.tile(np.atleast_1d(self.bounds[0, :].squeeze()), self.q)
+        u_bounds = np.tile(np.atleast_1d(self.bounds[1, :].squeeze()), self.q)
+        return l_bounds, u_bounds
+
+    def _optimize_halton_device(self, model, n_samples):
+        """Analytic q == 1 path with the candidates generated ON the device (``gpx_halton``:
+        SciPy's scrambled Halton points bit for bit, scaled to the bounds and pushed through the
+        model's ScaleTransform in the same kernel) and swept by the fused ``gpx_predict_acq``;
+        only the winner's coordinates and value return to the host.  Returns None when the model
+        or its input transform needs the host path."""
+        from . import engine as E
+        from .transforms import EPSILON, IdentityTransform, ScaleTransform
+
+        t = getattr(model, "input_transform", None)
+        if model.x is None or not isinstance(t, (IdentityTransform, ScaleTransform)):
+            return None
+        key, _ = state.get_rng_key()
+        halton = qmc.Halton(d=self.bounds.shape[1] * self.q, seed=key)      # draws the permutations
+        if not hasattr(halton, "_permutations") or not hasattr(halton, "num_generated"):
+            return None
+        lb, ub = self._bounds_tiled()
+        if isinstance(t, ScaleTransform):
+            t_min, t_span = t._minima.reshape(-1), (t._maxima - t._minima + EPSILON).reshape(-1)
+        else:
+            t_min = t_span = None
+        raw, xt = E.halton(halton, n_samples, lb, ub, t_min, t_span)
+        if state.verbose > 1:
+            unit = (raw.cpu().numpy() - lb) / (ub - lb)
+            print(f"qmc discrepancy (sample quality index) = {qmc.discrepancy(unit):.02e}")
+        acq, beta, y_max = self._device_spec(model)
+        _, _, _, val, idx = model._acquire(None, self.fast, acq, beta=beta, y_max=y_max,
+                                           want_arrays=False, x_new_t_dev=xt)
+        return raw[idx].cpu().numpy().reshape(self.q, -1), val
+
     def _optimize_halton(self, model, n_samples):
         """gpax/acquisition.py:166-216: best of ``n_samples`` Halton points.
 
@@ -122,6 +157,12 @@ class AcquisitionFunction:
         path evaluates all candidates in one fused device sweep, so any ``n_samples`` is
         accepted; for multiples of ``batch_threshold`` the result is the reference's (same
         Halton points, same first-maximum rule)."""
+        if not (self.force_monte_carlo or self.q > 1) and hasattr(model, "_acquire"):
+            saved = state.rng_key
+            out = self._optimize_halton_device(model, n_samples)
+            if out is not None:
+                return out
+            state.rng_key = saved          # host path below re-draws the same key
         samples = self._halton(n_samples)
         if self.force_monte_carlo or self.q > 1:
             vals = np.concatenate([

@@ -272,7 +272,61 @@ argmax_finalize_kernel(int64_t P, const double *__restrict__ part_val,
     }
 }
 
+// Scrambled Halton candidates (gpax/acquisition.py:184-200: qmc.Halton(d, seed).random(n), qmc.scale
+// to the bounds, then the model's input transform), one thread per (point, dimension).  SciPy's
+// sequence (scipy/stats/_qmc_cy.pyx, Owen's randomised Halton) for index i in base b with the
+// digit permutations P[j][.] it draws from the seed:
+//     x = 0; b2r = 1/b; q = i;  for j: r = q % b; x += P[j][r] * b2r; b2r /= b; q = (q - r) / b
+// in exactly this operation order (this file is compiled with -fmad=false, so nothing is fused):
+// the points are bit-identical to SciPy's.  meta[3 q .. 3 q + 2] = (base, number of digit rows,
+// offset of dimension q's table in perm).  raw = x * (upper - lower) + lower (qmc.scale);
+// xt = (raw - t_min) / t_span * 2 + (-1) (ScaleTransform.forward, gpax/transforms.py:254-258;
+// t_min == NULL: identity).
+__global__ void __launch_bounds__(256)
+halton_kernel(int64_t n, int d, int64_t start, const int32_t *__restrict__ meta,
+              const int32_t *__restrict__ perm, const double *__restrict__ lower,
+              const double *__restrict__ upper, const double *__restrict__ t_min,
+              const double *__restrict__ t_span, double *__restrict__ raw, double *__restrict__ xt) {
+    const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= n * d) return;
+    const int64_t i = e / d;
+    const int q = (int)(e % d);
+    const int64_t base = meta[3 * q];
+    const int rows = meta[3 * q + 1];
+    const int32_t *P = perm + meta[3 * q + 2];
+    int64_t quo = start + i;
+    double x = 0.0, b2r = 1.0 / (double)base;
+    for (int j = 0; j < rows; ++j) {
+        const int64_t rem = quo % base;
+        x = x + (double)P[(int64_t)j * base + rem] * b2r;
+        b2r = b2r / (double)base;
+        quo = (quo - rem) / base;
+    }
+    const double r = x * (upper[q] - lower[q]) + lower[q];
+    if (raw) raw[e] = r;
+    if (xt) xt[e] = t_min ? (r - t_min[q]) / t_span[q] * 2.0 + (-1.0) : r;
+}
+
 }  // namespace gpx
+
+extern "C" int gpx_halton(int64_t n, int32_t d, int64_t start_index, const int32_t *meta,
+                          const int32_t *perm, const double *lower, const double *upper,
+                          const double *t_min, const double *t_span, double *raw, double *xt,
+                          void *stream) {
+    using namespace gpx;
+    GPX_ARG_CHECK(n >= 0, 1);
+    GPX_ARG_CHECK(d >= 1 && d <= 1024, 2);
+    GPX_ARG_CHECK(start_index >= 0, 3);
+    GPX_ARG_CHECK(meta != nullptr && perm != nullptr, 4);
+    GPX_ARG_CHECK(lower != nullptr && upper != nullptr, 6);
+    GPX_ARG_CHECK((t_min == nullptr) == (t_span == nullptr), 8);
+    if (n == 0) return 0;
+    halton_kernel<<<(unsigned)((n * d + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
+        n, d, start_index, meta, perm, lower, upper, t_min, t_span, raw, xt);
+    count_launches(1);
+    GPX_LAUNCH_CHECK();
+    return 0;
+}
 
 extern "C" int64_t gpx_acq_parts(int64_t M) { return (M + gpx::A_CW - 1) / gpx::A_CW; }
 

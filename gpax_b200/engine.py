@@ -265,6 +265,34 @@ def draw(hpd: HyperParams, x, x_new, W, mu, G, key, diag_noise=None, partitionab
     return y, info
 
 
+def halton(sampler, n, lower, upper, t_min=None, t_span=None, dev=None, want_raw=True):
+    """``gpx_halton``: the points ``sampler.random(n)`` of a seeded ``scipy.stats.qmc.Halton`` would
+    return, scaled to ``[lower, upper]`` (and through a ScaleTransform), generated on the device.
+    Returns ``(raw [n, d] or None, xt [n, d])``.  Advances ``sampler.num_generated`` like SciPy."""
+    dev = _require_cuda(dev)
+    bases = [int(b) for b in sampler.base]
+    d = len(bases)
+    perms = [np.ascontiguousarray(np.asarray(p, dtype=np.int64)) for p in sampler._permutations]
+    if any(p.ndim != 2 or p.shape[1] != b for p, b in zip(perms, bases)):
+        raise RuntimeError("unexpected layout of scipy.stats.qmc.Halton._permutations")
+    meta, off = [], 0
+    for p, b in zip(perms, bases):
+        meta += [b, p.shape[0], off]
+        off += p.size
+    meta_t = torch.tensor(meta, dtype=torch.int32, device=dev)
+    perm_t = torch.from_numpy(np.concatenate([p.ravel() for p in perms]).astype(np.int32)).to(dev)
+    lo = _dev(np.broadcast_to(np.asarray(lower, float).reshape(-1), (d,)).copy(), dev)
+    hi = _dev(np.broadcast_to(np.asarray(upper, float).reshape(-1), (d,)).copy(), dev)
+    tm = None if t_min is None else _dev(np.asarray(t_min, float).reshape(d), dev)
+    ts = None if t_span is None else _dev(np.asarray(t_span, float).reshape(d), dev)
+    raw = torch.empty((n, d), dtype=F64, device=dev) if want_raw else None
+    xt = torch.empty((n, d), dtype=F64, device=dev)
+    check(lib.gpx_halton(int(n), d, int(sampler.num_generated), _ptr(meta_t), _ptr(perm_t), _ptr(lo), _ptr(hi),
+                         _ptr(tm), _ptr(ts), _ptr(raw), _ptr(xt), _stream()), "gpx_halton")
+    sampler.num_generated += int(n)
+    return raw, xt
+
+
 def argmax_finalize(pv, pi):
     dev = pv.device
     bv = torch.empty(1, dtype=F64, device=dev)

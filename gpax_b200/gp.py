@@ -311,16 +311,31 @@ class GaussianProcess:
         hp = {k: np.atleast_1d(v) for k, v in hp.items()}
         return GPSample(hp=hp, y=y, mu=mu_h, sd=sd_h)
 
-    def _acquire(self, x_new, fast, acq, beta=10.0, y_max=0.0, want_arrays=True):
+    def _acquire(self, x_new, fast, acq, beta=10.0, y_max=0.0, want_arrays=True, x_new_t_dev=None):
         """Fused moments -> reverse transform -> acquisition -> argmax on the device
         (gpax/gp.py:76-90 + gpax/acquisition.py:211-216,260-266,291-298).
-        Returns ``(mu, sd, acq values, best value, best index)``."""
+        Returns ``(mu, sd, acq values, best value, best index)``.  ``x_new_t_dev``: candidates
+        that already live on the device in kernel (transformed) space (``gpx_halton``); only a
+        conditioned model takes them, and only a non-constant mean brings them to the host."""
         from . import engine as E
 
-        x_new_t = self.input_transform.forward(np.asarray(x_new, float), transforms_as="mean")
         _, rng = state.get_rng_key()
         hp, _ = self._hp_for(rng, fast)
         a, b, c = _affine_of(self.output_transform)
+        if x_new_t_dev is not None:
+            if self.x is None:
+                raise ValueError("device-resident candidates need a conditioned model")
+            post = self._posterior(hp)
+            if isinstance(self.mean, ConstantMean):
+                kw = {"m_const": float(self.mean.mean)}
+            else:                      # user Python: evaluate it where it can run
+                kw = self._m_new_kw(x_new_t_dev.cpu().numpy(), hp)
+            o_mu, o_sd, o_acq, bv, bi = post.predict_acq(
+                x_new_t_dev, acq, beta=beta, y_max=y_max, mu_scale=a, mu_shift=b, sd_scale=c,
+                observation_noise=self.observation_noise, want_arrays=want_arrays, **kw)
+            host = [None if t is None else t.cpu().numpy() for t in (o_mu, o_sd, o_acq)]
+            return host[0], host[1], host[2], float(bv.item()), int(bi.item())
+        x_new_t = self.input_transform.forward(np.asarray(x_new, float), transforms_as="mean")
         if self.x is not None:
             # conditioned model: one fused gpx_predict_acq sweep, no [S, M] moment buffers
             post = self._posterior(hp)

@@ -42,7 +42,7 @@
 extern "C" {
 #endif
 
-#define GPX_ABI_VERSION 6
+#define GPX_ABI_VERSION 7
 
 /* covariance families: gpax/kernels.py:110 (RBF), :129 (Matern nu=5/2), :150 (Periodic) */
 enum { GPX_RBF = 0, GPX_MATERN52 = 1, GPX_PERIODIC = 2 };
@@ -204,6 +204,18 @@ int gpx_acq_reduce(int64_t S, int64_t M, const double *mu, const double *var,
                    double *part_val, int64_t *part_idx, void *stream);
 int gpx_argmax_finalize(int64_t P, const double *part_val, const int64_t *part_idx,
                         double *best_val, int64_t *best_idx, void *stream);
+
+/* gpx_halton: the scrambled Halton candidate set of _optimize_halton
+ * (gpax/acquisition.py:184-200: qmc.Halton(d, seed=key).random(n) -> qmc.scale(bounds) -> the
+ * model's input transform, gpax/gp.py:438) generated on the device, bit-identical to SciPy's
+ * points.  The digit permutations are what SciPy draws from the seed (a few hundred int32; the
+ * caller takes them from the seeded qmc.Halton object and uploads them once):
+ *   meta [3 d] int32: per dimension (base, digit rows, offset of its [rows, base] table in perm);
+ *   lower/upper [d]: bounds; t_min/t_span [d]: ScaleTransform minima and (max - min + 1e-8), or
+ *   both NULL (identity);  raw [n, d] (bounds space) and xt [n, d] (kernel space), either nullable. */
+int gpx_halton(int64_t n, int32_t d, int64_t start_index, const int32_t *meta, const int32_t *perm,
+               const double *lower, const double *upper, const double *t_min, const double *t_span,
+               double *raw, double *xt, void *stream);
 
 /* ---------------------------------------------------------------------------
  * gpx_predict_acq: the fused posterior predictive + acquisition sweep over a

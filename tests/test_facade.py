@@ -537,3 +537,48 @@ def test_acquisition_signatures_follow_reference():
     assert (a.q, a.batch_threshold, a.fast, a.beta) == (2, 50, False, 3.0)
     d = inspect.signature(UpperConfidenceBound.__init__).parameters
     assert d["beta"].default == 10.0 and d["fast"].default is True and d["batch_threshold"].default == 100
+
+
+# ---------------------------------------------------------------------------
+# GPU: row N3 -- Halton candidates generated on the device
+# ---------------------------------------------------------------------------
+@pytest.mark.gpu
+@pytest.mark.parametrize("d,n", [(1, 1000), (2, 4096), (5, 777)])
+def test_device_halton_is_scipy_bit_for_bit(cuda, d, n):
+    import torch
+    from scipy.stats import qmc
+    from gpax_b200 import engine as E
+    rng = np.random.default_rng(d)
+    lo, hi = rng.uniform(-3, 0, d), rng.uniform(1, 4, d)
+    t = ScaleTransform()
+    t.fit(rng.uniform(-2, 3, (50, d)))
+    ref_sampler, dev_sampler = qmc.Halton(d=d, seed=987654321), qmc.Halton(d=d, seed=987654321)
+    for _ in range(2):                                   # second call continues the sequence
+        ref = qmc.scale(ref_sampler.random(n), lo, hi)
+        raw, xt = E.halton(dev_sampler, n, lo, hi, t._minima.reshape(-1),
+                           (t._maxima - t._minima + 1e-8).reshape(-1), dev=cuda)
+        torch.cuda.synchronize()
+        np.testing.assert_array_equal(raw.cpu().numpy(), ref)
+        np.testing.assert_array_equal(xt.cpu().numpy(), t.forward(ref, transforms_as="mean"))
+    assert dev_sampler.num_generated == ref_sampler.num_generated == 2 * n
+    _, xi = E.halton(qmc.Halton(d=d, seed=5), 64, lo, hi, dev=cuda, want_raw=False)      # identity transform
+    np.testing.assert_array_equal(xi.cpu().numpy(), qmc.scale(qmc.Halton(d=d, seed=5).random(64), lo, hi))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("make", [lambda b: EI(bounds=b), lambda b: UCB(bounds=b, beta=4.0, fast=False)])
+def test_optimize_device_candidates_equal_host_path(cuda, make, monkeypatch):
+    rng = np.random.default_rng(8)
+    x = rng.uniform(-1, 1, (35, 2))
+    y = np.sin(3 * x[:, 0]) * np.cos(2 * x[:, 1]) + 0.01 * rng.normal(size=35)
+    gp = ExactGP(kernel=MaternKernel(), x=x, y=y, hp_samples=7)
+    acq = make(np.array([[-1.0, -1.0], [1.0, 1.0]]))
+    state.set_rng_key(77)
+    xb_dev, vb_dev = acq.optimize(gp, 3000)              # not a multiple of batch_threshold: accepted
+    end_key = state.rng_key
+    monkeypatch.setattr(type(acq), "_optimize_halton_device", lambda self, model, n: None)
+    state.set_rng_key(77)
+    xb_host, vb_host = acq.optimize(gp, 3000)
+    assert state.rng_key == end_key                      # both paths advance the key chain alike
+    np.testing.assert_array_equal(xb_dev, xb_host)
+    assert vb_dev == vb_host
