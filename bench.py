@@ -53,6 +53,9 @@ def parse():
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"])
     ap.add_argument("--cpu-samples", type=int, default=0, help="samples in the CPU baseline slice (0 = auto)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--exchange", default="peer", choices=["peer", "nccl"],
+                    help="N > 1 moment exchange: peer = predictive kernel stores straight into the reducing "
+                         "rank's HBM over NVLink (symmetric memory), nccl = all_to_all_single")
     ap.add_argument("--no-c3", action="store_true", help="skip the C3 (candidate-sharded acquisition sweep) leg")
     ap.add_argument("--c3-candidates", type=int, default=1_000_000)
     ap.add_argument("--c3-samples", type=int, default=2000)
@@ -79,6 +82,7 @@ def config_dict(args, wl, world):
                         "(gram+cholesky+alpha/mll+trtri+fused predictive+EI argmax)",
             "n": wl.n, "S_total": S_total, "S_per_gpu": S_local, "M": wl.M, "d": wl.d, "kernel": wl.kind,
             "sharding": f"samples over {world} rank(s)", "l2": "inputs_exceed_l2"}
+
 
 
 # ---------------------------------------------------------------------------
@@ -323,6 +327,15 @@ def run_ours(args):
         xbuf = (torch.empty(world * S_local * my_cnt, dtype=torch.float64, device=dev),
                 torch.empty(world * S_local * my_cnt, dtype=torch.float64, device=dev))
     pws = E.predict_ws_alloc(S_local, n, d, dev)
+    peer, exchange = None, "none (1 rank)"
+    if world > 1:
+        exchange = "nccl all_to_all_single"
+        if args.exchange == "peer":
+            try:
+                peer = P.PeerMoments(S_local, M, dev)
+                exchange = "peer stores over NVLink (symmetric memory), 2 device barriers per step"
+            except Exception as e:      # reported in the JSON line, never silent
+                exchange = f"nccl all_to_all_single (peer exchange unavailable: {type(e).__name__}: {e})"[:300]
 
     def one_step(dev_inputs=None, timed_events=None):
         """The hot path.  dev_inputs: already-resident tensors (kernel-only leg) or
@@ -343,15 +356,25 @@ def run_ours(args):
         E.trtri(bufL, n, dinv, bufW)
         if timed_events is not None:
             timed_events["pred0"].record()
-        for eo, co, cnt in layout:                 # one block per reducing rank (one block at N = 1)
-            if cnt:
-                E.predict(hpd, di["x"], di["x_new"][co:co + cnt], bufW, alpha, hpd.jitter, None, 1.0, True, True,
-                          mu[eo:eo + S_local * cnt].view(S_local, cnt),
-                          var[eo:eo + S_local * cnt].view(S_local, cnt), pws)
+        if peer is not None:
+            peer.begin()
+            for co, cnt, mu_r, var_r in peer.targets:      # block r goes straight into rank r's HBM
+                if cnt:
+                    E.predict(hpd, di["x"], di["x_new"][co:co + cnt], bufW, alpha, hpd.jitter, None, 1.0, True,
+                              True, mu_r, var_r, pws)
+        else:
+            for eo, co, cnt in layout:             # one block per reducing rank (one block at N = 1)
+                if cnt:
+                    E.predict(hpd, di["x"], di["x_new"][co:co + cnt], bufW, alpha, hpd.jitter, None, 1.0, True,
+                              True, mu[eo:eo + S_local * cnt].view(S_local, cnt),
+                              var[eo:eo + S_local * cnt].view(S_local, cnt), pws)
         if timed_events is not None:
             timed_events["pred1"].record()
         # every candidate is reduced over ALL samples on one rank, in global sample order
-        mu_all, var_all, off = P.exchange_moments(mu, var, M=M, out=xbuf)
+        if peer is not None:
+            mu_all, var_all, off = peer.end()
+        else:
+            mu_all, var_all, off = P.exchange_moments(mu, var, M=M, out=xbuf)
         o_mu, o_sd, o_acq, pv, pi = E.acq_reduce(mu_all, var_all, _cabi.ACQ_EI, 0.0, y_max,
                                                  wl.out_std + 1e-8, wl.out_mean, wl.out_std, off)
         bv, bi = E.argmax_finalize(pv, pi)
@@ -431,7 +454,7 @@ def run_ours(args):
         parity = parity_block(wl, mu2[:ns].cpu().numpy(), var2[:ns].cpu().numpy(), mu_o, var_o, bi_ns.item())
 
     # free the C2 state before the C3 leg
-    del bufL, bufW, dinv, mu, var, pws, xbuf
+    del bufL, bufW, dinv, mu, var, pws, xbuf, peer
     torch.cuda.empty_cache()
     c3 = None if args.no_c3 else run_c3(args, torch, dist, E, P, _cabi, dev, world, rank)
 
@@ -464,6 +487,7 @@ def run_ours(args):
                          "frac_of_dgemm": chol_tflops / peak if peak else None,
                          "flops": "S*n^3/3", "peak": "self-measured cuBLAS DGEMM (as roofline.peak_source)"},
             "argmax": {"index": argmax_c2[0], "value": argmax_c2[1]},
+            "exchange": exchange,
         }
         if parity is not None:
             line["parity"] = parity
@@ -496,7 +520,7 @@ def run_c3(args, torch, dist, E, P, _cabi, dev, world, rank):
            "unit": "candidate x sample pairs/s", "scaling": "strong"}
     for name, acq, beta in (("ei", _cabi.ACQ_EI, 0.0), ("ucb", _cabi.ACQ_UCB, 10.0)):
         def sweep():
-            o = post.predict_acq(xn, acq, beta, y_max, a, b, c, m_offset=off, m_tile=8192, want_arrays=False)
+            o = post.predict_acq(xn, acq, beta, y_max, a, b, c, m_offset=off, want_arrays=False)
             bv, bi = o[3], o[4]
             if world > 1:
                 bv, bi = E.argmax_finalize(*P.all_gather_pairs(bv, bi))

@@ -853,11 +853,15 @@ extern "C" int gpx_predict(const gpx_kernel_params *kp, int64_t S, int64_t n, in
 // samples in the fixed order s = 0..S-1 right after they are produced.
 // ---------------------------------------------------------------------------
 extern "C" int64_t gpx_predict_acq_tile(int64_t S, int64_t M) {
-    // 16*S*m_tile bytes of moments <= 256 MiB (measured: within 2 % of the unbounded two-stage
-    // sweep at C3; 48 MiB, i.e. L2-resident, costs 8 % in launch tails), multiple of the
-    // acquisition block (256 candidates) so tile winners land on gpx_acq_parts(M) slots
+    // 16*S*m_tile bytes of moments <= 1 GiB, multiple of the acquisition block (256 candidates) so
+    // tile winners land on gpx_acq_parts(M) slots.  The moments of a tile cost one HBM round trip
+    // (C3: 32 GB in total = 4.6 ms of a 625 ms sweep), launch tails between tiles cost more: a
+    // 48 MiB (L2-resident) tile was 8 % slower and a 256 MiB tile 3.8 % slower than the unbounded
+    // two-stage sweep at C3 (profiles/r01/stage_timers_c3_c4_c5.log); GPX_ACQ_TILE_MIB overrides.
     if (S < 1) S = 1;
-    int64_t t = ((int64_t)256 << 20) / (16 * S);
+    static int64_t budget_mib = -1;
+    if (budget_mib < 0) { const char *e = getenv("GPX_ACQ_TILE_MIB"); budget_mib = (e && atoi(e) > 0) ? atoi(e) : 1024; }
+    int64_t t = (budget_mib << 20) / (16 * S);
     t = t / 256 * 256;
     if (t < 256) t = 256;
     const int64_t m_up = (M + 255) / 256 * 256;

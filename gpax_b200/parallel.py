@@ -112,3 +112,53 @@ def all_gather_pairs(best_val: torch.Tensor, best_idx: torch.Tensor, group=None)
     dist.all_gather_into_tensor(vals, best_val.contiguous(), group=group)
     dist.all_gather_into_tensor(idxs, best_idx.contiguous(), group=group)
     return vals, idxs
+
+
+class PeerMoments:
+    """Moment exchange WITHOUT a collective call: the receive buffers of all ranks are one
+    symmetric allocation (``torch.distributed._symmetric_memory``: peer-mapped over NVLink /
+    NVSwitch), and every rank's ``gpx_predict`` is handed, as its output pointers for candidate
+    block ``r``, the slot ``[rank * S_local, (rank + 1) * S_local) x cnt_r`` of RANK r's buffer.
+    The predictive kernel's own epilogue stores therefore ARE the transfer -- it overlaps the
+    compute tile by tile and nothing is staged locally or copied afterwards.  Two device-side
+    barriers on the launching stream order it: ``begin()`` (nobody overwrites a buffer that is
+    still being reduced) and ``end()`` (all peers' stores have landed) before ``gpx_acq_reduce``
+    reads ``mu_all / var_all [S_total, cnt_me]`` -- the same values in the same global sample
+    order as :func:`exchange_moments`, hence bit-identical results.
+
+    Raises at construction if symmetric memory is unavailable (callers then use
+    :func:`exchange_moments`; the choice is reported, never silent)."""
+
+    def __init__(self, S_local: int, M: int, device, group=None):
+        import torch.distributed._symmetric_memory as symm
+
+        world, rank = world_info()
+        if world < 2:
+            raise RuntimeError("PeerMoments needs an initialised process group with >= 2 ranks")
+        self.world, self.rank, self.S_local, self.M = world, rank, int(S_local), int(M)
+        self.layout = block_layout(S_local, M, world)
+        self.cnt_max = max(c for _, _, c in self.layout)
+        self.half = world * S_local * self.cnt_max                 # elements of the mu part (same on all ranks)
+        self.buf = symm.empty(2 * self.half, dtype=torch.float64, device=device)
+        self.hdl = symm.rendezvous(self.buf, dist.group.WORLD if group is None else group)
+        self.off, self.cnt = self.layout[rank][1], self.layout[rank][2]
+        # where THIS rank writes block r: rank r's buffer, rows [rank * S_local, ...) of its [S_total, cnt_r]
+        self.targets = []
+        for r, (_, co, cnt) in enumerate(self.layout):
+            if cnt == 0:
+                self.targets.append((co, 0, None, None))
+                continue
+            o = rank * S_local * cnt
+            mu_r = self.hdl.get_buffer(r, (S_local, cnt), torch.float64, o)
+            var_r = self.hdl.get_buffer(r, (S_local, cnt), torch.float64, self.half + o)
+            self.targets.append((co, cnt, mu_r, var_r))
+
+    def begin(self):
+        self.hdl.barrier(channel=0)
+
+    def end(self):
+        """-> ``(mu_all [S_total, cnt_me], var_all, offset)`` of this rank's candidate chunk."""
+        self.hdl.barrier(channel=1)
+        n = self.world * self.S_local * self.cnt
+        return (self.buf[:n].view(self.world * self.S_local, self.cnt),
+                self.buf[self.half:self.half + n].view(self.world * self.S_local, self.cnt), self.off)

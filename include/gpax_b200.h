@@ -224,10 +224,10 @@ int gpx_halton(int64_t n, int32_t d, int64_t start_index, const int32_t *meta, c
  * (gpax/gp.py:399-501) and what _optimize_halton (gpax/acquisition.py:203-214)
  * loops over in chunks of 100, here in one call.  Candidates are walked in tiles
  * of m_tile (multiple of 256; gpx_predict_acq_tile(S, M) picks the default: [S, m_tile]
- * moments of at most 256 MiB; pass a smaller one, 16*S*m_tile <= ~48 MiB, to keep them
- * L2-resident); per tile gpx_predict writes the per-sample moments into `ws` and
+ * moments of at most 1 GiB; pass a smaller one, 16*S*m_tile <= ~48 MiB, to keep them
+ * L2-resident at the price of more launch tails); per tile gpx_predict writes the per-sample moments into `ws` and
  * gpx_acq_reduce consumes them at once: K* never exists in HBM and no [S, M] moment
- * buffer is ever allocated (C3: 32 GB -> 256 MiB).
+ * buffer is ever allocated (C3: 32 GB -> 1 GiB).
  * Arguments are those of gpx_predict followed by those of gpx_acq_reduce;
  * part_val/part_idx [gpx_acq_parts(M)]; best_val/best_idx (nullable) receive the
  * first maximum over this call's M candidates (global index m_offset + j), ready

@@ -72,6 +72,25 @@ for eo, co, cn in layout:
         E.predict(p2.hpd, p2.x, xn2[co:co + cn], p2.W, p2.alpha, p2.hpd.jitter, None, 1.0, True, True,
                   mu[eo:eo + S_local * cn].view(S_local, cn), var[eo:eo + S_local * cn].view(S_local, cn))
 mu_all, var_all, off2 = P.exchange_moments(mu, var, M=M)
+# the same exchange by peer stores: gpx_predict writes each block straight into the reducing rank's buffer
+peer_status = "ok"
+try:
+    peer = P.PeerMoments(S_local, M, dev)
+except Exception as e:
+    peer, peer_status = None, f"unavailable ({type(e).__name__}: {e})"
+if peer is not None:
+    for rep in range(2):                       # twice: the begin() barrier protects the buffer being re-used
+        peer.begin()
+        for co, cn, mu_r, var_r in peer.targets:
+            if cn:
+                E.predict(p2.hpd, p2.x, xn2[co:co + cn], p2.W, p2.alpha, p2.hpd.jitter, None, 1.0, True, True,
+                          mu_r, var_r)
+        mu_p, var_p, off_p = peer.end()
+        torch.cuda.synchronize()
+        assert off_p == off2
+        assert torch.equal(mu_p, mu_all) and torch.equal(var_p, var_all), "peer-store exchange differs from all_to_all"
+if os.environ.get("GPX_REQUIRE_PEER") == "1":
+    assert peer is not None, peer_status
 y_max2 = float(w2.y_raw.max())
 a2, b2, c2 = w2.out_std + 1e-8, w2.out_mean, w2.out_std
 o_mu, o_sd, o_acq, pv, pi = E.acq_reduce(mu_all, var_all, _cabi.ACQ_EI, 0.0, y_max2, a2, b2, c2, off2)
@@ -91,4 +110,4 @@ if rank == 0:
         np.testing.assert_array_equal(got, ref.cpu().numpy())
 dist.barrier()
 dist.destroy_process_group()
-print(f"rank {rank} ok", flush=True)
+print(f"rank {rank} ok (peer exchange: {peer_status})", flush=True)
