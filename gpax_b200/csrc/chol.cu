@@ -213,8 +213,8 @@ tile_kernel(int64_t n, int p, double *__restrict__ A, int64_t lda, const double 
         const double *D = dinv + ((size_t)s * T + p) * NB * NB;
         Operand a{As, lda, i * NB, (int64_t)p * NB, n, n};
         Operand b{D, NB, 0, 0, NB, NB};
-        tile_gemm<false>(smem, a, b, NB, acc);
-        tile_store<false>(As, lda, i * NB, (int64_t)p * NB, n, n, 1.0, false, acc);
+        tile_gemm<false, false, 2>(smem, a, b, NB, acc);      // Dinv^T is upper: skip its zero k groups
+        tile_store<false, false, 2>(As, lda, i * NB, (int64_t)p * NB, n, n, 1.0, false, acc);
     } else if (OP == OP_TRTRI_ACC) {
         // W(p, j) = sum_{k=j..p-1} L(p,k) W(k,j), j = blockIdx.x  (A is W here)
         const int64_t j = blockIdx.x;
@@ -253,8 +253,8 @@ tile_kernel(int64_t n, int p, double *__restrict__ A, int64_t lda, const double 
         const double *D = dinv + ((size_t)s * T + p) * NB * NB;
         Operand a{D, NB, 0, 0, NB, NB};
         Operand b{As, lda, (int64_t)p * NB, j * NB, n, n};
-        tile_gemm<true>(smem, a, b, NB, acc);
-        tile_store<true>(As, lda, (int64_t)p * NB, j * NB, n, n, -1.0, false, acc);
+        tile_gemm<true, false, 1>(smem, a, b, NB, acc);       // Dinv is lower: skip its zero k groups
+        tile_store<true, false, 1>(As, lda, (int64_t)p * NB, j * NB, n, n, -1.0, false, acc);
     }
 }
 

@@ -172,12 +172,40 @@ __device__ __forceinline__ void tile_load_frags(unsigned sop, int base, int h, i
     }
 }
 
+// Triangular operands (the 128x128 inverse diagonal block Dinv, K = 128, tile origin 0):
+//   TRI = 1: A is lower triangular (A[m][k] = 0 for k > m; OP_TRTRI_FIN)
+//   TRI = 2: B^T is lower triangular (Bop[k][n] = 0 for k > n; OP_TRSM, B "NT")
+// An 8-wide k group k8 only meets the row fragments mi >= k8 - 8 wm (TRI 1) / the column
+// fragments ni >= k8 - 4 wn (TRI 2); the others multiply structural zeros.  They are skipped by
+// real warp-uniform branches into template-instantiated blocks (a predicated-off DMMA still
+// occupies the pipe for its 16 cycles), which removes 47 % of the DMMAs.
+// For TRI 2 the work grows with wn, and a warp's sub-partition is warp % 4 = its wn: the second
+// row of warps is mirrored (wn -> 3 - wn) so every sub-partition gets one light and one heavy warp.
+template <int TRI>
+__device__ __forceinline__ int warp_wn(int warp) {
+    return (TRI == 2 && (warp >> 2)) ? 3 - (warp & 3) : (warp & 3);
+}
+
+// DMMAs of one half slice (two k-steps) for the fragments mi >= MI0, ni >= NI0
+template <int MI0, int NI0>
+__device__ __forceinline__ void mma_half(double (&acc)[T_MF][T_NF][2], const double (&a)[T_MF][2],
+                                         const double (&b)[T_NF][2]) {
+#pragma unroll
+    for (int kk = 0; kk < 2; ++kk)
+#pragma unroll
+        for (int mi = MI0; mi < T_MF; ++mi)
+#pragma unroll
+            for (int ni = NI0; ni < T_NF; ++ni)
+                dmma884(acc[mi][ni][0], acc[mi][ni][1], a[mi][kk], b[ni][kk]);
+}
+
 // full main loop; smem = T_SMEM_BYTES of dynamic shared memory
-template <bool B_NN, bool A_T = false>
+template <bool B_NN, bool A_T = false, int TRI = 0>
 __device__ __forceinline__ void tile_gemm(double *smem, const Operand &A, const Operand &B,
                                           int64_t K, double (&acc)[T_MF][T_NF][2]) {
+    static_assert(TRI == 0 || (TRI == 1 && B_NN && !A_T) || (TRI == 2 && !B_NN && !A_T), "unsupported TRI shape");
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int wm = warp >> 2, wn = warp & 3;
+    const int wm = warp >> 2, wn = warp_wn<TRI>(warp);
     const int lr = lane >> 2, lc = lane & 3;
     const unsigned s0 = (unsigned)__cvta_generic_to_shared(smem);
     constexpr unsigned STAGE_B = T_STAGE_ELEMS * 8, OP_B = T_OP_ELEMS * 8;
@@ -217,16 +245,33 @@ __device__ __forceinline__ void tile_gemm(double *smem, const Operand &A, const 
         const unsigned sa = s0 + (unsigned)(it % TSTAGES) * STAGE_B, sb = sa + OP_B;
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
+            const int k8 = (int)it * 2 + h;                       // 8-wide k group of this half slice
+            const int first = TRI == 1 ? k8 - wm * 8 : (TRI == 2 ? k8 - wn * 4 : 0);
+            if (TRI != 0 && first >= (TRI == 1 ? T_MF : T_NF)) continue;   // nothing of this warp meets it
             double a[T_MF][2], b[T_NF][2];
             tile_load_frags<A_T, T_MF>(sa, wm * 64, h, lr, lc, a);
             tile_load_frags<B_NN, T_NF>(sb, wn * 32, h, lr, lc, b);
-#pragma unroll
-            for (int kk = 0; kk < 2; ++kk)
-#pragma unroll
-                for (int mi = 0; mi < T_MF; ++mi)
-#pragma unroll
-                    for (int ni = 0; ni < T_NF; ++ni)
-                        dmma884(acc[mi][ni][0], acc[mi][ni][1], a[mi][kk], b[ni][kk]);
+            if (TRI == 1) {
+                switch (first) {
+                    case 1: mma_half<1, 0>(acc, a, b); break;
+                    case 2: mma_half<2, 0>(acc, a, b); break;
+                    case 3: mma_half<3, 0>(acc, a, b); break;
+                    case 4: mma_half<4, 0>(acc, a, b); break;
+                    case 5: mma_half<5, 0>(acc, a, b); break;
+                    case 6: mma_half<6, 0>(acc, a, b); break;
+                    case 7: mma_half<7, 0>(acc, a, b); break;
+                    default: mma_half<0, 0>(acc, a, b); break;
+                }
+            } else if (TRI == 2) {
+                switch (first) {
+                    case 1: mma_half<0, 1>(acc, a, b); break;
+                    case 2: mma_half<0, 2>(acc, a, b); break;
+                    case 3: mma_half<0, 3>(acc, a, b); break;
+                    default: mma_half<0, 0>(acc, a, b); break;
+                }
+            } else {
+                mma_half<0, 0>(acc, a, b);
+            }
         }
     }
     cp_async_wait<0>();
@@ -234,12 +279,12 @@ __device__ __forceinline__ void tile_gemm(double *smem, const Operand &A, const 
 }
 
 // epilogue: C[(c_r0+m)*ldc + c_c0+n] = beta*C + alpha*acc for m,n inside limits
-template <bool B_NN, bool A_T = false>
+template <bool B_NN, bool A_T = false, int TRI = 0>
 __device__ __forceinline__ void tile_store(double *C, int64_t ldc, int64_t c_r0, int64_t c_c0,
                                            int64_t rows_lim, int64_t cols_lim, double alpha,
                                            bool accumulate, double (&acc)[T_MF][T_NF][2]) {
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int wm = warp >> 2, wn = warp & 3;
+    const int wm = warp >> 2, wn = warp_wn<TRI>(warp);
     const int lr = lane >> 2, lc = lane & 3;
     if (accumulate && c_r0 + TM <= rows_lim && c_c0 + TN <= cols_lim) {
         // interior read-modify-write tile: issue the 16 loads of four rows before the
