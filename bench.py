@@ -488,6 +488,8 @@ def run_ours(args):
                          "flops": "S*n^3/3", "peak": "self-measured cuBLAS DGEMM (as roofline.peak_source)"},
             "argmax": {"index": argmax_c2[0], "value": argmax_c2[1]},
             "exchange": exchange,
+            "cholesky_schedule": ["left-looking", "right-looking + look-ahead"][
+                _cabi.lib.gpx_potrf_schedule(S_local, n)],
         }
         if parity is not None:
             line["parity"] = parity

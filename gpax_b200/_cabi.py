@@ -51,6 +51,7 @@ SIGNATURES = {
     "gpx_gram": (C.c_int, [_kp, _i64, _i64, _i64, _ptr, _ptr, _ptr, _i64, _i64, _ptr, _i32,
                            _i32, _ptr, _i64, _ptr]),
     "gpx_dinv_bytes": (_sz, [_i64, _i64]),
+    "gpx_potrf_schedule": (_i32, [_i64, _i64]),
     "gpx_potrf_batched": (C.c_int, [_i64, _i64, _ptr, _i64, _ptr, _ptr, _ptr]),
     "gpx_trtri_batched": (C.c_int, [_i64, _i64, _ptr, _i64, _ptr, _ptr, _i64, _ptr]),
     "gpx_mll_ws_bytes": (_sz, [_i64, _i64]),

@@ -443,6 +443,11 @@ extern "C" size_t gpx_dinv_bytes(int64_t S, int64_t n) {
     return (size_t)S * T * GPX_NB * GPX_NB * sizeof(double);
 }
 
+extern "C" int32_t gpx_potrf_schedule(int64_t S, int64_t n) {
+    const int T = (int)((n + GPX_NB - 1) / GPX_NB);
+    return gpx::choose_left(S, T) ? 0 : 1;
+}
+
 extern "C" int gpx_potrf_batched(int64_t S, int64_t n, double *A, int64_t lda, double *dinv,
                                  int32_t *info, void *stream) {
     using namespace gpx;

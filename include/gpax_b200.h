@@ -99,6 +99,13 @@ int gpx_gram(const gpx_kernel_params *kp, int64_t S, int64_t n, int64_t m,
  *   blocks of L (used by the solves below).  info[S].
  */
 size_t gpx_dinv_bytes(int64_t S, int64_t n);
+/* Which blocked schedule gpx_potrf_batched / gpx_trtri_batched use for a batch of S matrices of
+ * order n: 0 = left-looking (deep-K updates; large batches), 1 = right-looking with look-ahead
+ * (few large matrices).  Both are backward stable but sum in a different order, so factors of
+ * the SAME matrix computed inside batches on either side of the threshold differ in the last
+ * bits (~1e-16 relative): results are bit-reproducible for a fixed local batch size, not across
+ * batch sizes that straddle the switch (GPX_CHOL_SCHEDULE=left|right pins it). */
+int32_t gpx_potrf_schedule(int64_t S, int64_t n);
 int gpx_potrf_batched(int64_t S, int64_t n, double *A, int64_t lda,
                       double *dinv, int32_t *info, void *stream);
 
