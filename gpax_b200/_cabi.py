@@ -87,7 +87,7 @@ for _name, (_res, _args) in SIGNATURES.items():
     _fn.restype = _res
     _fn.argtypes = _args
 
-ABI_VERSION = 7
+ABI_VERSION = 8
 if lib.gpx_abi_version() != ABI_VERSION:
     raise ImportError("libgpax_b200.so ABI version mismatch")
 

@@ -42,7 +42,7 @@
 extern "C" {
 #endif
 
-#define GPX_ABI_VERSION 7
+#define GPX_ABI_VERSION 8
 
 /* covariance families: gpax/kernels.py:110 (RBF), :129 (Matern nu=5/2), :150 (Periodic) */
 enum { GPX_RBF = 0, GPX_MATERN52 = 1, GPX_PERIODIC = 2 };
