@@ -7,7 +7,7 @@ mkdir -p "$out" "$here/obj"
 NVCC="${NVCC:-/usr/local/cuda/bin/nvcc}"
 FLAGS=(-gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -std=c++17 -Xcompiler -fPIC -Xptxas -v)
 pids=()
-for f in api gram chol mll predict acq mll_grad draw; do
+for f in api gram chol mll predict acq mll_grad draw predict_i8; do
   [ -f "$here/$f.cu" ] || continue
   # incremental: skip objects newer than their source, every header and this script
   if [ -z "${GPX_REBUILD:-}" ] && [ -f "$here/obj/$f.o" ] && \

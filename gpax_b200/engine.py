@@ -199,6 +199,28 @@ def predict(hpd: HyperParams, x, x_new, W, alpha, diag_add, m_new=None, m_const=
     return mu, var
 
 
+def predict_i8_ws_alloc(S, n, d, dev):
+    return torch.empty(max(1, lib.gpx_predict_i8_ws_bytes(S, n, d) // 8), dtype=F64, device=dev)
+
+
+def predict_i8(hpd: HyperParams, x, x_new, W, alpha, diag_add, m_new=None, m_const=1.0, mu=None, var=None,
+               ws=None, prepare=True):
+    """``gpx_predict_i8`` (EXPERIMENTAL): ``gpx_predict`` with the contraction emulated on the INT8
+    tensor cores (Ozaki splitting, 45 slice products); RBF / Matern, d <= 4, 128 < n <= 14000."""
+    S, n, M = hpd.S, x.shape[0], x_new.shape[0]
+    dev = x.device
+    if ws is None:
+        ws = predict_i8_ws_alloc(S, n, hpd.d, dev)
+    if mu is None:
+        mu = torch.empty((S, M), dtype=F64, device=dev)
+    if var is None:
+        var = torch.empty((S, M), dtype=F64, device=dev)
+    check(lib.gpx_predict_i8(C.byref(hpd.kp), S, n, M, _ptr(x), _ptr(x_new), _ptr(W), W.shape[2], _ptr(alpha),
+                             _ptr(m_new), float(m_const), _ptr(diag_add), _ptr(mu), _ptr(var),
+                             1 if prepare else 0, _ptr(ws), _stream()), "gpx_predict_i8")
+    return mu, var
+
+
 def acq_reduce(mu, var, acq, beta=10.0, y_max=0.0, mu_scale=1.0, mu_shift=0.0, sd_scale=1.0,
                m_offset=0, want_arrays=True):
     S, M = mu.shape

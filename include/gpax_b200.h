@@ -42,7 +42,7 @@
 extern "C" {
 #endif
 
-#define GPX_ABI_VERSION 8
+#define GPX_ABI_VERSION 9
 
 /* covariance families: gpax/kernels.py:110 (RBF), :129 (Matern nu=5/2), :150 (Periodic) */
 enum { GPX_RBF = 0, GPX_MATERN52 = 1, GPX_PERIODIC = 2 };
@@ -165,6 +165,21 @@ int gpx_predict(const gpx_kernel_params *kp, int64_t S, int64_t n, int64_t M,
                 const double *W, int64_t ldw, const double *alpha,
                 const double *m_new, double m_const, const double *diag_add,
                 double *mu, double *var, void *ws, void *stream);
+
+/* gpx_predict_i8 (EXPERIMENTAL): gpx_predict with the contraction V = W K*^T emulated on the INT8
+ * tensor cores (tcgen05.mma kind::i8, INT32 accumulators in TMEM) by Ozaki splitting: 9 int8
+ * slices per operand, the 45 slice products of weight p + q < 9 (the count BASELINE config 2 needs
+ * to match native FP64).  Same call site as gpx_predict (gpax/gp.py:277-301); only
+ * RBF / Matern-5/2, d <= 4, 128 < n <= 14000 (else -3).  Arguments of gpx_predict plus
+ *   prepare != 0: (re)build the per-factorisation data in ws (row exponents and int8 slices of
+ *                 W, staged training rows); pass 0 to sweep more candidates against the same W;
+ *   ws: gpx_predict_i8_ws_bytes(S, n, d) bytes (~9.4 n^2 / 2 per sample). */
+size_t gpx_predict_i8_ws_bytes(int64_t S, int64_t n, int32_t d);
+int gpx_predict_i8(const gpx_kernel_params *kp, int64_t S, int64_t n, int64_t M,
+                   const double *x, const double *xnew,
+                   const double *W, int64_t ldw, const double *alpha,
+                   const double *m_new, double m_const, const double *diag_add,
+                   double *mu, double *var, int32_t prepare, void *ws, void *stream);
 
 /* gpx_predict_static: gpx_predict WITHOUT a caller workspace, for callers that cannot
  * allocate (code under CUDA graph capture, tight serving loops, harnesses that forbid
