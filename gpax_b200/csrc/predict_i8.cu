@@ -3,27 +3,31 @@
 // accumulators in TMEM) by Ozaki splitting, for n > 128, RBF / Matern-5/2, d <= 4.  EXPERIMENTAL,
 // selected only by GPX_PREDICT_I8=1 / this entry point; gpx_predict (FP64 DMMA) stays the default.
 //
-// Numerics (tools/ozaki_feasibility.py).  Each fp64 operand is written as
-//   a = 2^e * sum_{p<9} s_p 2^-(6+7p),  s_0 in [-63,63], s_p in [-127,127]   (62 bits below 2^e)
-// with e per ROW of W (computed once per factorisation) and one e for K* (0 <= k* <= k_scale).
-// Slice products s^W_p s^K_q are exact in INT32; products of equal weight p + q = c are summed
-// exactly in the same accumulator "plane" c (|sum| <= 9 * n * 127^2 < 2^31 for n <= 14 000);
-// planes c < 9 are kept (45 slice products): measured error = native FP64's on BASELINE config 2
-// including its cond(K) ~ 3e7 samples; 8 planes (36 products) miss 1e-10 by 30-50x.
+// Numerics (tools/ozaki_feasibility.py).  Each fp64 operand becomes a 64-bit fixed-
+// point integer whose BYTES are the int8 slices (slicing costs nothing):
+//   W row i : X = floor(w * 2^(63 - e_i)) two's complement, e_i per ROW of W (once per
+//             factorisation); slice p = byte 7 - p, the top one signed, the others unsigned,
+//             weight 2^(e_i - 7 - 8p);
+//   K*      : Y = trunc(k * 2^(64 - e_K)), 0 <= k* <= k_scale < 2^e_K; slice q = byte 7 - q,
+//             unsigned, weight 2^(e_K - 8 - 8q).
+// Slice products are exact in INT32; products of equal weight p + q = c are summed exactly in the
+// same accumulator "plane" c (|sum| < 8 * n * 255^2 < 2^31 for n <= 4000; measured 0.11 * 2^31 at
+// n = 2048); planes c < 8 are kept (36 slice products): measured error = native FP64's on BASELINE
+// config 2 including its cond(K) ~ 3e7 samples; 7 planes (28 products) miss 1e-10 by 50-100x.
 //
-// Mapping.  CTA = (sample, 48 candidates); it walks the 128-row blocks of W top to bottom and,
+// Mapping.  CTA = (sample, 64 candidates); it walks the 128-row blocks of W top to bottom and,
 // per block, the 32-wide k chunks left of / on the diagonal:
-//   A (W slices)  : 9 canonical K-major [128 x 32] int8 tiles per chunk, pre-split once per
-//                   factorisation into one contiguous 36 KB block per (row block, chunk), bulk-
-//                   copied (cp.async.bulk + mbarrier) into a 4-stage ring together with the 32
+//   A (W slices)  : 8 canonical K-major [128 x 32] byte tiles per chunk, pre-split once per
+//                   factorisation into one contiguous 32 KB block per (row block, chunk), bulk-
+//                   copied (cp.async.bulk + mbarrier) into a 5-stage ring together with the 32
 //                   staged training rows the generator needs;
-//   B (K* slices) : generated on chip in fp64 (reference operation order), converted to 62-bit
-//                   fixed point, cut into 9 int8 slices STACKED along N ([9 x 48] x 32, double
-//                   buffered): one W slice p meets the K* slices q = 0..8-p in at most two MMAs
-//                   (N <= 240) whose output columns are the consecutive planes p..8 -- 13 MMAs per
-//                   chunk instead of 45 (a small-N UTCIMMA costs >= 34.5 ns whatever N is:
-//                   tools/probe/tcgen05_i8_probe.cu);
-//   D             : 9 planes x 48 columns = 432 of the 512 TMEM columns, lane = W row;
+//   B (K* slices) : generated on chip in fp64 (reference operation order) by 8 warps (two per SM
+//                   sub-partition), converted to fixed point, its bytes transposed with PRMT and
+//                   stored STACKED along N ([8 x 64] x 32, double buffered): one W slice p meets
+//                   the K* slices q = 0..7-p in at most two MMAs (N <= 256) whose output columns are
+//                   the consecutive planes p..7 -- 12 MMAs per chunk instead of 36 (a small-N
+//                   UTCIMMA costs >= 34.5 ns whatever N is: tools/probe/tcgen05_i8_probe.cu);
+//   D             : 8 planes x 64 columns = all 512 TMEM columns, lane = W row;
 //   epilogue      : per row block, tcgen05.ld -> fp64 Horner over the planes -> * 2^(e_row + e_K)
 //                   -> squared and accumulated per lane; the column sums are reduced once at the end.
 #include <cuda.h>
@@ -35,16 +39,18 @@ namespace i8 {
 
 constexpr int KC = 32;            // k per chunk = K of one UTCIMMA
 constexpr int MT = 128;           // W rows per block = M of the MMA = TMEM lanes
-constexpr int NT = 48;            // candidates per CTA
-constexpr int NSL = 9;            // int8 slices per operand
-constexpr int NPL = 9;            // accumulator planes kept (p + q < NPL)
+constexpr int NT = 64;            // candidates per CTA
+constexpr int NSL = 8;            // byte slices per operand
+constexpr int NPL = 8;            // accumulator planes kept (p + q < NPL)
 constexpr int A_TILE = MT * KC;                    // bytes of one slice tile
-constexpr int A_BLOCK = NSL * A_TILE;              // 36 864 bytes per (row block, chunk)
-constexpr int B_ROWS = NSL * NT;                   // 432 stacked rows
-constexpr int B_TILE = B_ROWS * KC;                // 13 824 bytes
+constexpr int A_BLOCK = NSL * A_TILE;              // 32 768 bytes per (row block, chunk)
+constexpr int B_ROWS = NSL * NT;                   // 512 stacked rows
+constexpr int B_TILE = B_ROWS * KC;                // 16 384 bytes
 constexpr int A_STAGES = 4;
-constexpr int THREADS = 256;
-constexpr int GEN_THREADS = 192;                   // warps 0..5 generate; warp 6 lane 0 loads, warp 7 lane 0 issues MMAs
+constexpr int NB = 4;                              // K* slice buffers (the gen -> MMA -> commit -> gen hand-off is ~2 us)                         // loads run this many chunks ahead of the MMAs
+constexpr int GEN_WARPS = 8;                       // warps 0..7 generate K* and run the epilogue
+constexpr int GEN_THREADS = GEN_WARPS * 32;
+constexpr int THREADS = GEN_THREADS + 64;          // warp 8 lane 0: MMA issue; warp 9 lane 0: bulk loads
 
 // canonical K-major SWIZZLE_NONE operand layout: 8 x 16-byte core matrices, cores along M/N every
 // 128 bytes (SBO), the two 16-byte halves of K = 32 every (rows / 8) * 128 bytes (LBO)
@@ -70,7 +76,7 @@ w_rowexp_kernel(int n, int n128, const double *__restrict__ W, int64_t ldw, int3
     if (lane == 0) ew[(size_t)s * n128 + row] = mx > 0.0 ? ilogb(mx) + 1 : 0;
 }
 
-// one CTA = one (row block, chunk) of one sample: 128 x 32 values -> 9 canonical int8 tiles
+// one CTA = one (row block, chunk) of one sample: 128 x 32 values -> 8 canonical byte tiles
 __global__ void __launch_bounds__(256)
 w_slice_kernel(int n, int n128, const double *__restrict__ W, int64_t ldw, const int32_t *__restrict__ ew,
                int8_t *__restrict__ out, int64_t sample_stride) {
@@ -87,20 +93,19 @@ w_slice_kernel(int n, int n128, const double *__restrict__ W, int64_t ldw, const
         const int row = rb * MT + r, col = kc * KC + k;
         double v = 0.0;
         if (row < n && col <= row) v = W[((size_t)s * n + row) * ldw + col];
-        double rres = scalbn(v, -ew[(size_t)s * n128 + row]);
+        // |v| < 2^e  ->  two's complement 64-bit fixed point; its bytes are the slices
+        const long long X = __double2ll_rd(scalbn(v, 63 - ew[(size_t)s * n128 + row]));
         const int o = canon_off(r, k, MT);
 #pragma unroll
-        for (int p = 0; p < NSL; ++p) {
-            rres *= (p == 0 ? 64.0 : 128.0);
-            const double sl = trunc(rres);
-            rres -= sl;
-            blk[p * A_TILE + o] = (int8_t)(int)sl;
-        }
+        for (int p = 0; p < NSL; ++p) blk[p * A_TILE + o] = (int8_t)(unsigned char)((unsigned long long)X >> (56 - 8 * p));
     }
 }
 
-// staged training rows: xs[s][k][0..DMAX-1] = x_k / length_s, [DMAX] = squared norm, [DMAX+1] = alpha
-// (zero rows for k >= n: finite covariances that meet zero W columns and alpha = 0)
+// staged training rows, component-major per 32-wide chunk: xs[s][k / 32][q][k % 32] with q < DMAX the
+// coordinates x_k / length_s, q = DMAX the squared norm, q = DMAX + 1 alpha (zeros for k >= n: finite
+// covariances that meet zero W columns and alpha = 0).  A generator thread needs four consecutive k
+// of every component: 32 contiguous bytes, and the 8 k-groups of a warp tile a 256-byte line --
+// conflict-free, where row-major rows (128 bytes apart) were an 8-way bank conflict on every load.
 template <int DMAX>
 __global__ void __launch_bounds__(256)
 xs_prep_kernel(gpx_kernel_params kp, int n, int n128, const double *__restrict__ x,
@@ -108,16 +113,16 @@ xs_prep_kernel(gpx_kernel_params kp, int n, int n128, const double *__restrict__
     const int64_t s = blockIdx.y;
     const int k = blockIdx.x * 256 + threadIdx.x;
     if (k >= n128) return;
-    double *dst = xs + ((size_t)s * n128 + k) * (DMAX + 2);
+    double *dst = xs + ((size_t)s * n128 + (size_t)(k / KC) * KC) * (DMAX + 2) + (k % KC);
     double nrm = 0.0;
 #pragma unroll
     for (int q = 0; q < DMAX; ++q) {
         double v = (k < n && q < kp.d) ? x[(size_t)k * kp.d + q] / len_of(kp, s, q) : 0.0;
-        dst[q] = v;
+        dst[q * KC] = v;
         nrm += v * v;
     }
-    dst[DMAX] = nrm;
-    dst[DMAX + 1] = k < n ? alpha[(size_t)s * n + k] : 0.0;
+    dst[DMAX * KC] = nrm;
+    dst[(DMAX + 1) * KC] = k < n ? alpha[(size_t)s * n + k] : 0.0;
 }
 
 
@@ -154,9 +159,11 @@ __device__ __forceinline__ uint64_t make_desc(uint32_t saddr, uint32_t lbo_bytes
     return (uint64_t)((saddr >> 4) & 0x3FFF) | ((uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16) |
            ((uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32) | ((uint64_t)1 << 46);
 }
-// instruction descriptor (cute::UMMA::InstrDescriptor): dense, S32 accumulators, signed int8 A and B, K-major
-__device__ __forceinline__ uint32_t make_idesc(int N) {
-    return (2u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(MT >> 4) << 24);
+// instruction descriptor (cute::UMMA::InstrDescriptor): dense, S32 accumulators, A signed or unsigned
+// bytes, B unsigned bytes, both K-major
+__device__ __forceinline__ uint32_t make_idesc(int N, bool a_signed) {
+    return (2u << 4) | ((a_signed ? 1u : 0u) << 7) | (0u << 10) | ((uint32_t)(N >> 3) << 17) |
+           ((uint32_t)(MT >> 4) << 24);
 }
 __device__ __forceinline__ void mma_i8(uint32_t tmem_d, uint64_t da, uint64_t db, uint32_t idesc, uint32_t accumulate) {
     asm volatile(
@@ -178,9 +185,9 @@ struct Cfg {
     static constexpr int XB = KC * XSP * 8;                                   // staged rows per chunk (bytes)
     static constexpr size_t OFF_X = (size_t)A_STAGES * A_BLOCK;
     static constexpr size_t OFF_B = OFF_X + (size_t)A_STAGES * XB;
-    static constexpr size_t OFF_RED = OFF_B + 2 * (size_t)B_TILE;             // [4][NT] colsum partials + [NT] means
-    static constexpr size_t OFF_BAR = OFF_RED + (5 * NT) * 8;
-    static constexpr size_t BYTES = OFF_BAR + 16 * 8 + 16 + 128 /*alignment slack*/;
+    static constexpr size_t OFF_RED = OFF_B + NB * (size_t)B_TILE;             // [8 warps][32] colsum partials + [NT] means
+    static constexpr size_t OFF_BAR = OFF_RED + (GEN_WARPS * 32 + NT) * 8;
+    static constexpr size_t BYTES = OFF_BAR + (2 * A_STAGES + 2 * NB + 2) * 8 + 16 + 128 /*alignment slack*/;
 };
 
 template <int KIND, int DMAX>
@@ -189,7 +196,9 @@ predict_i8_kernel(gpx_kernel_params kp, int n, int n128, int M, const double *__
                   const double *__restrict__ xnew, const int8_t *__restrict__ wsl, int64_t wsl_stride,
                   const int32_t *__restrict__ ew, const double *__restrict__ m_new, double m_const,
                   const double *__restrict__ diag_add, double *__restrict__ mu, double *__restrict__ var,
-                  int64_t ldo, int64_t ldmn) {
+                  int64_t ldo, int64_t ldmn, int dbg) {
+    // dbg (GPX_I8_DEBUG, profiling only): bit 0 skips the generator arithmetic, bit 1 the MMAs,
+    // bit 2 the epilogue arithmetic, bit 3 the fixed-point conversion + byte stores
     using C = Cfg<DMAX>;
     constexpr int XSP = C::XSP;
     extern __shared__ unsigned char smem_raw[];
@@ -199,9 +208,9 @@ predict_i8_kernel(gpx_kernel_params kp, int n, int n128, int M, const double *__
     unsigned char *sB = sm + C::OFF_B;
     double *sRed = reinterpret_cast<double *>(sm + C::OFF_RED);
     uint64_t *bars = reinterpret_cast<uint64_t *>(sm + C::OFF_BAR);
-    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 16);
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 2 * A_STAGES + 2 * NB + 2);
     const uint32_t b_fullA = smem_u32(bars), b_emptyA = b_fullA + 8 * A_STAGES, b_fullB = b_emptyA + 8 * A_STAGES,
-                   b_emptyB = b_fullB + 16, b_accFull = b_emptyB + 16, b_accEmpty = b_accFull + 8;
+                   b_emptyB = b_fullB + 8 * NB, b_accFull = b_emptyB + 8 * NB, b_accEmpty = b_accFull + 8;
 
     const int s = blockIdx.y, j0 = blockIdx.x * NT;
     const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
@@ -215,15 +224,15 @@ predict_i8_kernel(gpx_kernel_params kp, int n, int n128, int M, const double *__
             mbar_init(b_fullA + 8 * i, 1);
             mbar_init(b_emptyA + 8 * i, 1);
         }
-        for (int i = 0; i < 2; ++i) {
-            mbar_init(b_fullB + 8 * i, GEN_THREADS / 32);
+        for (int i = 0; i < NB; ++i) {
+            mbar_init(b_fullB + 8 * i, GEN_WARPS);
             mbar_init(b_emptyB + 8 * i, 1);
         }
         mbar_init(b_accFull, 1);
-        mbar_init(b_accEmpty, 4);
+        mbar_init(b_accEmpty, GEN_WARPS);
         asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
     }
-    if (warp == 7) {
+    if (warp == GEN_WARPS) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;\n" ::"r"(smem_u32(tmem_slot)) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;\n" ::: "memory");
     }
@@ -232,45 +241,57 @@ predict_i8_kernel(gpx_kernel_params kp, int n, int n128, int M, const double *__
     tc_fence_after();
     const uint32_t tmem = *tmem_slot;
 
-    if (warp == 6) {
-        // ---- producer: W slice blocks (stored in walk order) + the chunk's 32 staged rows ----
+    if (warp == GEN_WARPS + 1) {
+        // ---- producer thread: W slice blocks (stored in walk order) + the chunk's 32 staged rows ----
         if (lane == 0) {
             const int8_t *src = wsl + (int64_t)s * wsl_stride;
             const double *xs_s = xs + (size_t)s * n128 * XSP;
             int rb = 0, kc = 0;
             for (int g = 0; g < NCH; ++g) {
                 const int st = g % A_STAGES;
-                mbar_wait(b_emptyA + 8 * st, ((g / A_STAGES) & 1) ^ 1);
-                mbar_arrive_expect_tx(b_fullA + 8 * st, A_BLOCK + C::XB);
-                bulk_load(smem_u32(sA + (size_t)st * A_BLOCK), src + (int64_t)g * A_BLOCK, A_BLOCK, b_fullA + 8 * st);
+                mbar_wait(b_emptyA + 8 * st, ((g / A_STAGES) & 1) ^ 1);       // MMAs of chunk g - A_STAGES retired
+                mbar_arrive_expect_tx(b_fullA + 8 * st, ((dbg & 16) ? 0 : A_BLOCK) + C::XB);
+                if (!(dbg & 16))
+                    bulk_load(smem_u32(sA + (size_t)st * A_BLOCK), src + (int64_t)g * A_BLOCK, A_BLOCK, b_fullA + 8 * st);
                 bulk_load(smem_u32(sX + (size_t)st * KC * XSP), xs_s + (size_t)kc * KC * XSP, C::XB, b_fullA + 8 * st);
                 if (++kc == 4 * (rb + 1)) { kc = 0; ++rb; }
             }
         }
-    } else if (warp == 7) {
-        // ---- MMA issuer: per chunk, W slice p against the stacked K* slices q = 0 .. 8 - p ----
+    } else if (warp == GEN_WARPS) {
+        // ---- MMA issuer.  ONE thread issues everything, so its per-chunk instruction count is the
+        // floor of the chunk time: the 12 MMAs are fully unrolled and every descriptor is one add away
+        // from a per-chunk base (the 14-bit address field counts 16-byte units and cannot carry).
         if (lane == 0) {
-            uint32_t idesc[6];
-            for (int q = 1; q <= 5; ++q) idesc[q] = make_idesc(NT * q);
+            const uint64_t descA0 = make_desc(smem_u32(sA), (MT / 8) * 128, 128);
+            const uint64_t descB0 = make_desc(smem_u32(sB), (B_ROWS / 8) * 128, 128);
+            const uint32_t iu1 = make_idesc(NT * 1, false), iu2 = make_idesc(NT * 2, false), iu3 = make_idesc(NT * 3, false),
+                           iu4 = make_idesc(NT * 4, false), is4 = make_idesc(NT * 4, true);
             int g = 0;
             for (int rb = 0; rb < T; ++rb) {
                 if (rb > 0) mbar_wait(b_accEmpty, (rb - 1) & 1);       // the epilogue has drained the planes
                 for (int kc = 0; kc < 4 * (rb + 1); ++kc, ++g) {
-                    const int st = g % A_STAGES, buf = g & 1;
+                    const int st = g % A_STAGES, buf = g % NB;
                     mbar_wait(b_fullA + 8 * st, (g / A_STAGES) & 1);
-                    mbar_wait(b_fullB + 8 * buf, (g >> 1) & 1);
+                    mbar_wait(b_fullB + 8 * buf, (g / NB) & 1);
                     tc_fence_after();
-                    const uint32_t aBase = smem_u32(sA + (size_t)st * A_BLOCK), bBase = smem_u32(sB + (size_t)buf * B_TILE);
-                    for (int p = 0; p < NSL; ++p) {
-                        const uint64_t da = make_desc(aBase + p * A_TILE, (MT / 8) * 128, 128);
-                        int nq = NPL - p, q0 = 0;
-                        while (nq > 0) {
-                            const int take = nq < 5 ? nq : 5;
-                            const uint64_t db = make_desc(bBase + q0 * (NT / 8) * 128, (B_ROWS / 8) * 128, 128);
-                            mma_i8(tmem + (uint32_t)((p + q0) * NT), da, db, idesc[take], (kc > 0 || p > 0) ? 1u : 0u);
-                            q0 += take;
-                            nq -= take;
-                        }
+                    if (!(dbg & 2)) {
+                        const uint64_t a0 = descA0 + (uint64_t)(st * (A_BLOCK >> 4));
+                        const uint64_t b0 = descB0 + (uint64_t)(buf * (B_TILE >> 4));
+                        const uint32_t acc0 = kc > 0 ? 1u : 0u;
+                        constexpr uint64_t AS = A_TILE >> 4, BS = ((NT / 8) * 128) >> 4;     // descriptor steps per slice
+                        // W slice p (byte 7 - p; the top one signed) x stacked K* slices q0.. -> planes p + q0..
+                        mma_i8(tmem + 0 * NT, a0 + 0 * AS, b0 + 0 * BS, is4, acc0);       // p = 0: planes 0..3
+                        mma_i8(tmem + 4 * NT, a0 + 0 * AS, b0 + 4 * BS, is4, acc0);       //        planes 4..7
+                        mma_i8(tmem + 1 * NT, a0 + 1 * AS, b0 + 0 * BS, iu4, 1u);         // p = 1: planes 1..4
+                        mma_i8(tmem + 5 * NT, a0 + 1 * AS, b0 + 4 * BS, iu3, 1u);         //        planes 5..7
+                        mma_i8(tmem + 2 * NT, a0 + 2 * AS, b0 + 0 * BS, iu4, 1u);         // p = 2: planes 2..5
+                        mma_i8(tmem + 6 * NT, a0 + 2 * AS, b0 + 4 * BS, iu2, 1u);         //        planes 6..7
+                        mma_i8(tmem + 3 * NT, a0 + 3 * AS, b0 + 0 * BS, iu4, 1u);         // p = 3: planes 3..6
+                        mma_i8(tmem + 7 * NT, a0 + 3 * AS, b0 + 4 * BS, iu1, 1u);         //        plane 7
+                        mma_i8(tmem + 4 * NT, a0 + 4 * AS, b0 + 0 * BS, iu4, 1u);         // p = 4: planes 4..7
+                        mma_i8(tmem + 5 * NT, a0 + 5 * AS, b0 + 0 * BS, iu3, 1u);         // p = 5: planes 5..7
+                        mma_i8(tmem + 6 * NT, a0 + 6 * AS, b0 + 0 * BS, iu2, 1u);         // p = 6: planes 6..7
+                        mma_i8(tmem + 7 * NT, a0 + 7 * AS, b0 + 0 * BS, iu1, 1u);         // p = 7: plane 7
                     }
                     tc_commit(b_emptyA + 8 * st);       // frees the W stage ...
                     tc_commit(b_emptyB + 8 * buf);      // ... and the K* buffer when these MMAs retire
@@ -279,12 +300,13 @@ predict_i8_kernel(gpx_kernel_params kp, int n, int n128, int M, const double *__
             }
         }
     } else {
-        // ---- generator (warps 0..5) + epilogue (warps 0..3) ----
-        const int kq = t & 7, cb = t >> 3;                 // k = 4 kq .. 4 kq + 3; candidates cb, cb + 24
+        // ---- generator + epilogue (warps 0..7; sub-partition = warp % 4 hosts two of them) --------
+        const int kq = t & 7, cb = t >> 3;                 // k = 4 kq .. 4 kq + 3; candidates cb, cb + 32
+        const int quarter = warp & 3, half = warp >> 2;    // epilogue: TMEM lanes 32 quarter .., candidates 32 half ..
         double z[2][DMAX + 1];
 #pragma unroll
         for (int i = 0; i < 2; ++i) {
-            const int gj = j0 + cb + 24 * i;
+            const int gj = j0 + cb + 32 * i;
             double nrm = 0.0;
 #pragma unroll
             for (int q = 0; q < DMAX; ++q) {
@@ -294,21 +316,26 @@ predict_i8_kernel(gpx_kernel_params kp, int n, int n128, int M, const double *__
             }
             z[i][DMAX] = nrm;
         }
-        const double fx_scale = scalbn(1.0, 62 - ek);
+        const double fx_scale = scalbn(1.0, 64 - ek);
         double macc[2] = {0.0, 0.0};
-        double colsum[NT];
+        double colsum[32];
 #pragma unroll
-        for (int j = 0; j < NT; ++j) colsum[j] = 0.0;
+        for (int j = 0; j < 32; ++j) colsum[j] = 0.0;
 
         auto epilogue = [&](int rb) {
-            if (warp >= 4) return;
             mbar_wait(b_accFull, rb & 1);
             tc_fence_after();
-            const int row = rb * MT + warp * 32 + lane;
-            const double sc = scalbn(1.0, ew[(size_t)s * n128 + row] + ek - 12);
-            const uint32_t tl = tmem + ((uint32_t)(warp * 32) << 16);
+            if (dbg & 4) {
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(b_accEmpty);
+                return;
+            }
+            const int row = rb * MT + quarter * 32 + lane;
+            const double sc = scalbn(1.0, ew[(size_t)s * n128 + row] + ek - 15);
+            const uint32_t tl = tmem + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(half * 32);
 #pragma unroll
-            for (int jg = 0; jg < NT / 8; ++jg) {
+            for (int jg = 0; jg < 4; ++jg) {
                 int32_t a[NPL][8];
 #pragma unroll
                 for (int c = 0; c < NPL; ++c) ldtm_x8(tl + (uint32_t)(c * NT + jg * 8), a[c]);
@@ -317,7 +344,7 @@ predict_i8_kernel(gpx_kernel_params kp, int n, int n128, int M, const double *__
                 for (int q = 0; q < 8; ++q) {
                     double v = (double)a[NPL - 1][q];
 #pragma unroll
-                    for (int c = NPL - 2; c >= 0; --c) v = fma(v, 0.0078125, (double)a[c][q]);
+                    for (int c = NPL - 2; c >= 0; --c) v = fma(v, 0.00390625, (double)a[c][q]);
                     v *= sc;
                     colsum[jg * 8 + q] = fma(v, v, colsum[jg * 8 + q]);
                 }
@@ -329,14 +356,18 @@ predict_i8_kernel(gpx_kernel_params kp, int n, int n128, int M, const double *__
 
         int rb = 0, kc = 0, pending = -1, since = 0;       // pending: row block whose epilogue is deferred
         for (int g = 0; g < NCH; ++g) {
-            const int st = g % A_STAGES, buf = g & 1;
+            const int st = g % A_STAGES, buf = g % NB;
             mbar_wait(b_fullA + 8 * st, (g / A_STAGES) & 1);
             double xr[4][XSP];
-            const double *rowp = sX + (size_t)st * KC * XSP + (size_t)(4 * kq) * XSP;
+            const double2 *colp = reinterpret_cast<const double2 *>(sX + (size_t)st * KC * XSP + 4 * kq);
 #pragma unroll
-            for (int r = 0; r < 4; ++r)
-#pragma unroll
-                for (int q = 0; q < XSP; ++q) xr[r][q] = rowp[r * XSP + q];
+            for (int q = 0; q < XSP; ++q) {
+                const double2 lo2 = colp[q * (KC / 2)], hi2 = colp[q * (KC / 2) + 1];
+                xr[0][q] = lo2.x;
+                xr[1][q] = lo2.y;
+                xr[2][q] = hi2.x;
+                xr[3][q] = hi2.y;
+            }
             double v[2][4];
 #pragma unroll
             for (int i = 0; i < 2; ++i) {
@@ -348,7 +379,7 @@ predict_i8_kernel(gpx_kernel_params kp, int n, int n128, int M, const double *__
                     const double r2 = (z[i][DMAX] - 2.0 * xz) + xr[r][DMAX];
                     v[i][r] = r2 < 0.0 ? 0.0 : r2;
                 }
-                k_from_r2_vec<KIND, 4>(v[i], scale);
+                if (!(dbg & 1)) k_from_r2_vec<KIND, 4>(v[i], scale);
             }
             if (rb == T - 1) {
 #pragma unroll
@@ -356,23 +387,27 @@ predict_i8_kernel(gpx_kernel_params kp, int n, int n128, int M, const double *__
 #pragma unroll
                     for (int r = 0; r < 4; ++r) macc[i] = fma(v[i][r], xr[r][DMAX + 1], macc[i]);
             }
-            mbar_wait(b_emptyB + 8 * buf, ((g >> 1) & 1) ^ 1);          // MMAs of chunk g - 2 have read this buffer
+            mbar_wait(b_emptyB + 8 * buf, ((g / NB) & 1) ^ 1);          // MMAs of chunk g - NB have read this buffer
             unsigned char *bt = sB + (size_t)buf * B_TILE;
 #pragma unroll
             for (int i = 0; i < 2; ++i) {
-                unsigned long long fx[4];
+                if (dbg & 8) break;
+                uint32_t hi[4], lo[4];
 #pragma unroll
-                for (int r = 0; r < 4; ++r) fx[r] = __double2ull_rz(v[i][r] * fx_scale);
-                const int cand = cb + 24 * i;
+                for (int r = 0; r < 4; ++r) {
+                    const unsigned long long fx = __double2ull_rz(v[i][r] * fx_scale);
+                    hi[r] = (uint32_t)(fx >> 32);
+                    lo[r] = (uint32_t)fx;
+                }
+                const int cand = cb + 32 * i;
 #pragma unroll
                 for (int q = 0; q < NSL; ++q) {
-                    uint32_t w = 0;
-#pragma unroll
-                    for (int r = 0; r < 4; ++r) {
-                        const uint32_t sl = q == 0 ? (uint32_t)(fx[r] >> 56) : (uint32_t)((fx[r] >> (56 - 7 * q)) & 127ull);
-                        w |= sl << (8 * r);
-                    }
-                    *reinterpret_cast<uint32_t *>(bt + canon_off(q * NT + cand, 4 * kq, B_ROWS)) = w;
+                    // slice q = byte 7 - q of the fixed-point value; gather it from the 4 k values of this thread
+                    const uint32_t *w = q < 4 ? hi : lo;
+                    const uint32_t b = 3u - (uint32_t)(q & 3);
+                    const uint32_t sel = b | ((4u + b) << 4);
+                    const uint32_t p01 = __byte_perm(w[0], w[1], sel), p23 = __byte_perm(w[2], w[3], sel);
+                    *reinterpret_cast<uint32_t *>(bt + canon_off(q * NT + cand, 4 * kq, B_ROWS)) = __byte_perm(p01, p23, 0x5410);
                 }
             }
             fence_async_smem();
@@ -384,14 +419,12 @@ predict_i8_kernel(gpx_kernel_params kp, int n, int n128, int M, const double *__
         if (pending >= 0) epilogue(pending);
 
         // ---- results: column sums over the 128 lanes (= rows) of every block, means over k ----
-        if (warp < 4) {
 #pragma unroll
-            for (int j = 0; j < NT; ++j) {
-                double c = colsum[j];
+        for (int j = 0; j < 32; ++j) {
+            double c = colsum[j];
 #pragma unroll
-                for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
-                if (lane == 0) sRed[warp * NT + j] = c;
-            }
+            for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+            if (lane == 0) sRed[warp * 32 + j] = c;
         }
 #pragma unroll
         for (int i = 0; i < 2; ++i) {
@@ -399,7 +432,7 @@ predict_i8_kernel(gpx_kernel_params kp, int n, int n128, int M, const double *__
             m += __shfl_xor_sync(0xffffffffu, m, 1);
             m += __shfl_xor_sync(0xffffffffu, m, 2);
             m += __shfl_xor_sync(0xffffffffu, m, 4);
-            if (kq == 0) sRed[4 * NT + cb + 24 * i] = m;
+            if (kq == 0) sRed[GEN_WARPS * 32 + cb + 32 * i] = m;
         }
     }
     tc_fence_before();
@@ -408,13 +441,15 @@ predict_i8_kernel(gpx_kernel_params kp, int n, int n128, int M, const double *__
         const int gj = j0 + t;
         if (gj < M) {
             const double kd = k_from_r2<KIND>(0.0, scale);
-            const double cs = (sRed[t] + sRed[NT + t]) + (sRed[2 * NT + t] + sRed[3 * NT + t]);
+            const double *pr = sRed + (t >> 5) * 4 * 32 + (t & 31);       // the four lane-quarter warps of this half
+            const double cs = (pr[0] + pr[32]) + (pr[64] + pr[96]);
             if (var) var[(size_t)s * ldo + gj] = (kd + diag_add[s]) - cs;
-            if (mu) mu[(size_t)s * ldo + gj] = (m_new ? m_new[(size_t)s * ldmn + gj] : m_const) + sRed[4 * NT + t];
+            if (mu) mu[(size_t)s * ldo + gj] = (m_new ? m_new[(size_t)s * ldmn + gj] : m_const) + sRed[GEN_WARPS * 32 + t];
         }
     }
-    if (warp == 7) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;\n" ::"r"(tmem) : "memory");
+    if (warp == GEN_WARPS) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;\n" ::"r"(tmem) : "memory");
 }
+
 }  // namespace i8
 }  // namespace gpx
 
@@ -441,7 +476,7 @@ I8Layout i8_layout(int64_t S, int64_t n, int dmax) {
     return L;
 }
 int i8_supported(const gpx_kernel_params *kp, int64_t n) {
-    return (kp->kind == GPX_RBF || kp->kind == GPX_MATERN52) && kp->d <= 4 && n > 128 && n <= 14000;
+    return (kp->kind == GPX_RBF || kp->kind == GPX_MATERN52) && kp->d <= 4 && n > 128 && n <= 4000;
 }
 
 template <int KIND, int DMAX>
@@ -460,10 +495,12 @@ int launch_i8(const gpx_kernel_params *kp, int64_t S, int64_t n, int64_t M, cons
         w_slice_kernel<<<dim3((unsigned)L.nch, (unsigned)S), 256, 0, st>>>((int)n, (int)L.n128, W, ldw, ew, wsl, L.wsl_stride);
         count_launches(3);
     }
+    static int dbg = -1;
+    if (dbg < 0) { const char *e = getenv("GPX_I8_DEBUG"); dbg = e ? atoi(e) : 0; }
     if (int e = ensure_smem(predict_i8_kernel<KIND, DMAX>, Cfg<DMAX>::BYTES)) return e;
     dim3 grid((unsigned)((M + NT - 1) / NT), (unsigned)S);
     predict_i8_kernel<KIND, DMAX><<<grid, THREADS, Cfg<DMAX>::BYTES, st>>>(
-        *kp, (int)n, (int)L.n128, (int)M, xs, xnew, wsl, L.wsl_stride, ew, m_new, m_const, diag_add, mu, var, M, M);
+        *kp, (int)n, (int)L.n128, (int)M, xs, xnew, wsl, L.wsl_stride, ew, m_new, m_const, diag_add, mu, var, M, M, dbg);
     count_launches(1);
     return 0;
 }
@@ -483,7 +520,7 @@ extern "C" int gpx_predict_i8(const gpx_kernel_params *kp, int64_t S, int64_t n,
     GPX_ARG_CHECK(validate_kp(kp) == 0, 1);
     GPX_ARG_CHECK(S >= 0 && S <= 65535, 2);
     if (!i8_supported(kp, n)) {
-        set_error("gpx_predict_i8: only RBF / Matern-5/2 with d <= 4 and 128 < n <= 14000 (got kind %d, d %d, n %lld); "
+        set_error("gpx_predict_i8: only RBF / Matern-5/2 with d <= 4 and 128 < n <= 4000 (got kind %d, d %d, n %lld); "
                   "use gpx_predict", kp->kind, kp->d, (long long)n);
         return -3;
     }

@@ -167,13 +167,13 @@ int gpx_predict(const gpx_kernel_params *kp, int64_t S, int64_t n, int64_t M,
                 double *mu, double *var, void *ws, void *stream);
 
 /* gpx_predict_i8 (EXPERIMENTAL): gpx_predict with the contraction V = W K*^T emulated on the INT8
- * tensor cores (tcgen05.mma kind::i8, INT32 accumulators in TMEM) by Ozaki splitting: 9 int8
- * slices per operand, the 45 slice products of weight p + q < 9 (the count BASELINE config 2 needs
- * to match native FP64).  Same call site as gpx_predict (gpax/gp.py:277-301); only
- * RBF / Matern-5/2, d <= 4, 128 < n <= 14000 (else -3).  Arguments of gpx_predict plus
+ * tensor cores (tcgen05.mma kind::i8, INT32 accumulators in TMEM) by Ozaki splitting: the 8 bytes
+ * of a 64-bit fixed-point value per operand, the 36 slice products of weight p + q < 8 (the count
+ * BASELINE config 2 needs to match native FP64).  Same call site as gpx_predict (gpax/gp.py:277-301); only
+ * RBF / Matern-5/2, d <= 4, 128 < n <= 4000 (else -3).  Arguments of gpx_predict plus
  *   prepare != 0: (re)build the per-factorisation data in ws (row exponents and int8 slices of
  *                 W, staged training rows); pass 0 to sweep more candidates against the same W;
- *   ws: gpx_predict_i8_ws_bytes(S, n, d) bytes (~9.4 n^2 / 2 per sample). */
+ *   ws: gpx_predict_i8_ws_bytes(S, n, d) bytes (~8.5 n^2 / 2 per sample). */
 size_t gpx_predict_i8_ws_bytes(int64_t S, int64_t n, int32_t d);
 int gpx_predict_i8(const gpx_kernel_params *kp, int64_t S, int64_t n, int64_t M,
                    const double *x, const double *xnew,
