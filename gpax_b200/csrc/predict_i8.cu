@@ -46,8 +46,9 @@ constexpr int A_TILE = MT * KC;                    // bytes of one slice tile
 constexpr int A_BLOCK = NSL * A_TILE;              // 32 768 bytes per (row block, chunk)
 constexpr int B_ROWS = NSL * NT;                   // 512 stacked rows
 constexpr int B_TILE = B_ROWS * KC;                // 16 384 bytes
-constexpr int A_STAGES = 4;
-constexpr int NB = 4;                              // K* slice buffers (the gen -> MMA -> commit -> gen hand-off is ~2 us)                         // loads run this many chunks ahead of the MMAs
+constexpr int STAGES = 4;                          // ring of (W slice block + K* slice chunk) stages: loads run 3 chunks ahead
+constexpr int STAGE_BYTES = A_BLOCK + B_TILE;      // 49 152
+constexpr int MAX_T = 32;                          // row blocks: n <= 4096
 constexpr int GEN_WARPS = 8;                       // warps 0..7 generate K* and run the epilogue
 constexpr int GEN_THREADS = GEN_WARPS * 32;
 constexpr int THREADS = GEN_THREADS + 64;          // warp 8 lane 0: MMA issue; warp 9 lane 0: bulk loads
@@ -179,59 +180,57 @@ __device__ __forceinline__ void ldtm_x8(uint32_t taddr, int32_t (&r)[8]) {
 }
 __device__ __forceinline__ void ldtm_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;\n" ::: "memory"); }
 
-template <int DMAX>
+__device__ __forceinline__ void mbar_inval(uint32_t bar) {
+    asm volatile("mbarrier.inval.shared::cta.b64 [%0];\n" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ uint32_t mbar_test(uint32_t bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile(
+        "{\n .reg .pred p;\n mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n selp.u32 %0, 1, 0, p;\n}\n"
+        : "=r"(ok)
+        : "r"(bar), "r"(parity)
+        : "memory");
+    return ok;
+}
+// generic-proxy writes (global or shared) -> visible to the async proxy (bulk copies) once ordered by a barrier
+__device__ __forceinline__ void fence_async_all() { asm volatile("fence.proxy.async;\n" ::: "memory"); }
+
 struct Cfg {
-    static constexpr int XSP = DMAX + 2;
-    static constexpr int XB = KC * XSP * 8;                                   // staged rows per chunk (bytes)
-    static constexpr size_t OFF_X = (size_t)A_STAGES * A_BLOCK;
-    static constexpr size_t OFF_B = OFF_X + (size_t)A_STAGES * XB;
-    static constexpr size_t OFF_RED = OFF_B + NB * (size_t)B_TILE;             // [8 warps][32] colsum partials + [NT] means
+    static constexpr size_t OFF_RED = (size_t)STAGES * STAGE_BYTES;            // [8 warps][32] colsum partials + [NT] means
     static constexpr size_t OFF_BAR = OFF_RED + (GEN_WARPS * 32 + NT) * 8;
-    static constexpr size_t BYTES = OFF_BAR + (2 * A_STAGES + 2 * NB + 2) * 8 + 16 + 128 /*alignment slack*/;
+    static constexpr int NBAR = 2 * STAGES + MAX_T + 2;                         // full / empty per stage, gen per row block, accFull / accEmpty
+    static constexpr size_t BYTES = OFF_BAR + NBAR * 8 + 16 + 128 /*alignment slack*/;
 };
 
+// Persistent: CTA b walks the units (sample, 64 candidates) b, b + grid, ...; consecutive units share the
+// sample, so the CTAs running at any moment read the same W slice blocks out of L2.
 template <int KIND, int DMAX>
 __global__ void __launch_bounds__(THREADS, 1)
-predict_i8_kernel(gpx_kernel_params kp, int n, int n128, int M, const double *__restrict__ xs,
+predict_i8_kernel(gpx_kernel_params kp, int n, int n128, int M, int S, const double *__restrict__ xs,
                   const double *__restrict__ xnew, const int8_t *__restrict__ wsl, int64_t wsl_stride,
-                  const int32_t *__restrict__ ew, const double *__restrict__ m_new, double m_const,
-                  const double *__restrict__ diag_add, double *__restrict__ mu, double *__restrict__ var,
-                  int64_t ldo, int64_t ldmn, int dbg) {
+                  const int32_t *__restrict__ ew, unsigned char *__restrict__ scratch, int64_t scratch_stride,
+                  const double *__restrict__ m_new, double m_const, const double *__restrict__ diag_add,
+                  double *__restrict__ mu, double *__restrict__ var, int64_t ldo, int64_t ldmn, int dbg) {
     // dbg (GPX_I8_DEBUG, profiling only): bit 0 skips the generator arithmetic, bit 1 the MMAs,
-    // bit 2 the epilogue arithmetic, bit 3 the fixed-point conversion + byte stores
-    using C = Cfg<DMAX>;
-    constexpr int XSP = C::XSP;
+    // bit 2 the epilogue arithmetic, bit 3 the fixed-point conversion + byte stores, bit 4 the W loads
+    using C = Cfg;
+    constexpr int XSP = DMAX + 2;
     extern __shared__ unsigned char smem_raw[];
     unsigned char *sm = smem_raw + ((128u - (smem_u32(smem_raw) & 127u)) & 127u);
-    unsigned char *sA = sm;
-    double *sX = reinterpret_cast<double *>(sm + C::OFF_X);
-    unsigned char *sB = sm + C::OFF_B;
     double *sRed = reinterpret_cast<double *>(sm + C::OFF_RED);
     uint64_t *bars = reinterpret_cast<uint64_t *>(sm + C::OFF_BAR);
-    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 2 * A_STAGES + 2 * NB + 2);
-    const uint32_t b_fullA = smem_u32(bars), b_emptyA = b_fullA + 8 * A_STAGES, b_fullB = b_emptyA + 8 * A_STAGES,
-                   b_emptyB = b_fullB + 8 * NB, b_accFull = b_emptyB + 8 * NB, b_accEmpty = b_accFull + 8;
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + C::NBAR);
+    const uint32_t s_stage = smem_u32(sm);
+    const uint32_t b_full = smem_u32(bars), b_empty = b_full + 8 * STAGES, b_gen = b_empty + 8 * STAGES,
+                   b_accFull = b_gen + 8 * MAX_T, b_accEmpty = b_accFull + 8;
 
-    const int s = blockIdx.y, j0 = blockIdx.x * NT;
     const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
-    const int T = n128 / MT;
-    const int NCH = (int)chunks_before(T);
-    const double scale = kp.scale[s];
-    const int ek = ilogb(scale) + 1;                      // 0 <= k* <= scale < 2^ek
+    const int T = n128 / MT;                              // row blocks (<= MAX_T)
+    const int NKC = 4 * T;                                // k chunks
+    const int tiles = (M + NT - 1) / NT;
+    const int64_t units = (int64_t)S * tiles;
+    unsigned char *scr = scratch + (int64_t)blockIdx.x * scratch_stride;      // this CTA's K* slice store (L2-resident)
 
-    if (t == 0) {
-        for (int i = 0; i < A_STAGES; ++i) {
-            mbar_init(b_fullA + 8 * i, 1);
-            mbar_init(b_emptyA + 8 * i, 1);
-        }
-        for (int i = 0; i < NB; ++i) {
-            mbar_init(b_fullB + 8 * i, GEN_WARPS);
-            mbar_init(b_emptyB + 8 * i, 1);
-        }
-        mbar_init(b_accFull, 1);
-        mbar_init(b_accEmpty, GEN_WARPS);
-        asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
-    }
     if (warp == GEN_WARPS) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;\n" ::"r"(smem_u32(tmem_slot)) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;\n" ::: "memory");
@@ -241,212 +240,236 @@ predict_i8_kernel(gpx_kernel_params kp, int n, int n128, int M, const double *__
     tc_fence_after();
     const uint32_t tmem = *tmem_slot;
 
-    if (warp == GEN_WARPS + 1) {
-        // ---- producer thread: W slice blocks (stored in walk order) + the chunk's 32 staged rows ----
-        if (lane == 0) {
-            const int8_t *src = wsl + (int64_t)s * wsl_stride;
-            const double *xs_s = xs + (size_t)s * n128 * XSP;
-            int rb = 0, kc = 0;
-            for (int g = 0; g < NCH; ++g) {
-                const int st = g % A_STAGES;
-                mbar_wait(b_emptyA + 8 * st, ((g / A_STAGES) & 1) ^ 1);       // MMAs of chunk g - A_STAGES retired
-                mbar_arrive_expect_tx(b_fullA + 8 * st, ((dbg & 16) ? 0 : A_BLOCK) + C::XB);
-                if (!(dbg & 16))
-                    bulk_load(smem_u32(sA + (size_t)st * A_BLOCK), src + (int64_t)g * A_BLOCK, A_BLOCK, b_fullA + 8 * st);
-                bulk_load(smem_u32(sX + (size_t)st * KC * XSP), xs_s + (size_t)kc * KC * XSP, C::XB, b_fullA + 8 * st);
-                if (++kc == 4 * (rb + 1)) { kc = 0; ++rb; }
+    for (int64_t u = blockIdx.x; u < units; u += gridDim.x) {
+        const int s = (int)(u / tiles), j0 = (int)(u % tiles) * NT;
+        const double scale = kp.scale[s];
+        const int ek = ilogb(scale) + 1;                  // 0 <= k* <= scale < 2^ek
+        // every barrier starts the unit in phase 0 (all of them are quiescent here: the last epilogue
+        // waited for the last commit, which follows every earlier arrival)
+        if (t == 0) {
+            if (u != (int64_t)blockIdx.x)
+                for (int i = 0; i < C::NBAR; ++i) mbar_inval(b_full + 8 * i);
+            for (int i = 0; i < STAGES; ++i) {
+                mbar_init(b_full + 8 * i, 1);
+                mbar_init(b_empty + 8 * i, 1);
             }
+            for (int i = 0; i < MAX_T; ++i) mbar_init(b_gen + 8 * i, GEN_WARPS);
+            mbar_init(b_accFull, 1);
+            mbar_init(b_accEmpty, GEN_WARPS);
+            asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
         }
-    } else if (warp == GEN_WARPS) {
-        // ---- MMA issuer.  ONE thread issues everything, so its per-chunk instruction count is the
-        // floor of the chunk time: the 12 MMAs are fully unrolled and every descriptor is one add away
-        // from a per-chunk base (the 14-bit address field counts 16-byte units and cannot carry).
-        if (lane == 0) {
-            const uint64_t descA0 = make_desc(smem_u32(sA), (MT / 8) * 128, 128);
-            const uint64_t descB0 = make_desc(smem_u32(sB), (B_ROWS / 8) * 128, 128);
-            const uint32_t iu1 = make_idesc(NT * 1, false), iu2 = make_idesc(NT * 2, false), iu3 = make_idesc(NT * 3, false),
-                           iu4 = make_idesc(NT * 4, false), is4 = make_idesc(NT * 4, true);
-            int g = 0;
-            for (int rb = 0; rb < T; ++rb) {
-                if (rb > 0) mbar_wait(b_accEmpty, (rb - 1) & 1);       // the epilogue has drained the planes
-                for (int kc = 0; kc < 4 * (rb + 1); ++kc, ++g) {
-                    const int st = g % A_STAGES, buf = g % NB;
-                    mbar_wait(b_fullA + 8 * st, (g / A_STAGES) & 1);
-                    mbar_wait(b_fullB + 8 * buf, (g / NB) & 1);
-                    tc_fence_after();
-                    if (!(dbg & 2)) {
-                        const uint64_t a0 = descA0 + (uint64_t)(st * (A_BLOCK >> 4));
-                        const uint64_t b0 = descB0 + (uint64_t)(buf * (B_TILE >> 4));
-                        const uint32_t acc0 = kc > 0 ? 1u : 0u;
-                        constexpr uint64_t AS = A_TILE >> 4, BS = ((NT / 8) * 128) >> 4;     // descriptor steps per slice
-                        // W slice p (byte 7 - p; the top one signed) x stacked K* slices q0.. -> planes p + q0..
-                        mma_i8(tmem + 0 * NT, a0 + 0 * AS, b0 + 0 * BS, is4, acc0);       // p = 0: planes 0..3
-                        mma_i8(tmem + 4 * NT, a0 + 0 * AS, b0 + 4 * BS, is4, acc0);       //        planes 4..7
-                        mma_i8(tmem + 1 * NT, a0 + 1 * AS, b0 + 0 * BS, iu4, 1u);         // p = 1: planes 1..4
-                        mma_i8(tmem + 5 * NT, a0 + 1 * AS, b0 + 4 * BS, iu3, 1u);         //        planes 5..7
-                        mma_i8(tmem + 2 * NT, a0 + 2 * AS, b0 + 0 * BS, iu4, 1u);         // p = 2: planes 2..5
-                        mma_i8(tmem + 6 * NT, a0 + 2 * AS, b0 + 4 * BS, iu2, 1u);         //        planes 6..7
-                        mma_i8(tmem + 3 * NT, a0 + 3 * AS, b0 + 0 * BS, iu4, 1u);         // p = 3: planes 3..6
-                        mma_i8(tmem + 7 * NT, a0 + 3 * AS, b0 + 4 * BS, iu1, 1u);         //        plane 7
-                        mma_i8(tmem + 4 * NT, a0 + 4 * AS, b0 + 0 * BS, iu4, 1u);         // p = 4: planes 4..7
-                        mma_i8(tmem + 5 * NT, a0 + 5 * AS, b0 + 0 * BS, iu3, 1u);         // p = 5: planes 5..7
-                        mma_i8(tmem + 6 * NT, a0 + 6 * AS, b0 + 0 * BS, iu2, 1u);         // p = 6: planes 6..7
-                        mma_i8(tmem + 7 * NT, a0 + 7 * AS, b0 + 0 * BS, iu1, 1u);         // p = 7: plane 7
-                    }
-                    tc_commit(b_emptyA + 8 * st);       // frees the W stage ...
-                    tc_commit(b_emptyB + 8 * buf);      // ... and the K* buffer when these MMAs retire
-                }
-                tc_commit(b_accFull);
-            }
-        }
-    } else {
-        // ---- generator + epilogue (warps 0..7; sub-partition = warp % 4 hosts two of them) --------
-        const int kq = t & 7, cb = t >> 3;                 // k = 4 kq .. 4 kq + 3; candidates cb, cb + 32
-        const int quarter = warp & 3, half = warp >> 2;    // epilogue: TMEM lanes 32 quarter .., candidates 32 half ..
-        double z[2][DMAX + 1];
-#pragma unroll
-        for (int i = 0; i < 2; ++i) {
-            const int gj = j0 + cb + 32 * i;
-            double nrm = 0.0;
-#pragma unroll
-            for (int q = 0; q < DMAX; ++q) {
-                const double v = (gj < M && q < kp.d) ? xnew[(size_t)gj * kp.d + q] / len_of(kp, s, q) : 0.0;
-                z[i][q] = v;
-                nrm += v * v;
-            }
-            z[i][DMAX] = nrm;
-        }
-        const double fx_scale = scalbn(1.0, 64 - ek);
-        double macc[2] = {0.0, 0.0};
-        double colsum[32];
-#pragma unroll
-        for (int j = 0; j < 32; ++j) colsum[j] = 0.0;
+        __syncthreads();
+        tc_fence_after();
 
-        auto epilogue = [&](int rb) {
-            mbar_wait(b_accFull, rb & 1);
-            tc_fence_after();
-            if (dbg & 4) {
+        if (warp == GEN_WARPS + 1) {
+            // ---- producer thread: per chunk one W slice block (stored in walk order) + the chunk's K* slices
+            if (lane == 0) {
+                const int8_t *src = wsl + (int64_t)s * wsl_stride;
+                int g = 0;
+                for (int rb = 0; rb < T; ++rb) {
+                    mbar_wait(b_gen + 8 * rb, 0);                              // K* chunks 0 .. 4 rb + 3 are in the store
+                    for (int kc = 0; kc < 4 * (rb + 1); ++kc, ++g) {
+                        const int st = g % STAGES;
+                        mbar_wait(b_empty + 8 * st, ((g / STAGES) & 1) ^ 1);   // MMAs of chunk g - STAGES retired
+                        mbar_arrive_expect_tx(b_full + 8 * st, ((dbg & 16) ? 0 : A_BLOCK) + B_TILE);
+                        const uint32_t dst = s_stage + (uint32_t)st * STAGE_BYTES;
+                        if (!(dbg & 16)) bulk_load(dst, src + (int64_t)g * A_BLOCK, A_BLOCK, b_full + 8 * st);
+                        bulk_load(dst + A_BLOCK, scr + (size_t)kc * B_TILE, B_TILE, b_full + 8 * st);
+                    }
+                }
+            }
+        } else if (warp == GEN_WARPS) {
+            // ---- MMA issuer: 12 UTCIMMA per chunk, every descriptor one add away from a per-chunk base
+            if (lane == 0) {
+                const uint64_t descA0 = make_desc(s_stage, (MT / 8) * 128, 128);
+                const uint64_t descB0 = make_desc(s_stage + A_BLOCK, (B_ROWS / 8) * 128, 128);
+                const uint32_t iu1 = make_idesc(NT * 1, false), iu2 = make_idesc(NT * 2, false), iu3 = make_idesc(NT * 3, false),
+                               iu4 = make_idesc(NT * 4, false), is4 = make_idesc(NT * 4, true);
+                int g = 0;
+                for (int rb = 0; rb < T; ++rb) {
+                    if (rb > 0) {
+                        mbar_wait(b_accEmpty, (rb - 1) & 1);       // the epilogue has drained the planes
+                        tc_fence_after();
+                    }
+                    for (int kc = 0; kc < 4 * (rb + 1); ++kc, ++g) {
+                        const int st = g % STAGES;
+                        mbar_wait(b_full + 8 * st, (g / STAGES) & 1);
+                        tc_fence_after();
+                        if (!(dbg & 2)) {
+                            const uint64_t a0 = descA0 + (uint64_t)(st * (STAGE_BYTES >> 4));
+                            const uint64_t b0 = descB0 + (uint64_t)(st * (STAGE_BYTES >> 4));
+                            const uint32_t acc0 = kc > 0 ? 1u : 0u;
+                            constexpr uint64_t AS = A_TILE >> 4, BS = ((NT / 8) * 128) >> 4;     // descriptor steps per slice
+                            // W slice p (byte 7 - p; the top one signed) x stacked K* slices q0.. -> planes p + q0..
+                            mma_i8(tmem + 0 * NT, a0 + 0 * AS, b0 + 0 * BS, is4, acc0);       // p = 0: planes 0..3
+                            mma_i8(tmem + 4 * NT, a0 + 0 * AS, b0 + 4 * BS, is4, acc0);       //        planes 4..7
+                            mma_i8(tmem + 1 * NT, a0 + 1 * AS, b0 + 0 * BS, iu4, 1u);         // p = 1: planes 1..4
+                            mma_i8(tmem + 5 * NT, a0 + 1 * AS, b0 + 4 * BS, iu3, 1u);         //        planes 5..7
+                            mma_i8(tmem + 2 * NT, a0 + 2 * AS, b0 + 0 * BS, iu4, 1u);         // p = 2: planes 2..5
+                            mma_i8(tmem + 6 * NT, a0 + 2 * AS, b0 + 4 * BS, iu2, 1u);         //        planes 6..7
+                            mma_i8(tmem + 3 * NT, a0 + 3 * AS, b0 + 0 * BS, iu4, 1u);         // p = 3: planes 3..6
+                            mma_i8(tmem + 7 * NT, a0 + 3 * AS, b0 + 4 * BS, iu1, 1u);         //        plane 7
+                            mma_i8(tmem + 4 * NT, a0 + 4 * AS, b0 + 0 * BS, iu4, 1u);         // p = 4: planes 4..7
+                            mma_i8(tmem + 5 * NT, a0 + 5 * AS, b0 + 0 * BS, iu3, 1u);         // p = 5: planes 5..7
+                            mma_i8(tmem + 6 * NT, a0 + 6 * AS, b0 + 0 * BS, iu2, 1u);         // p = 6: planes 6..7
+                            mma_i8(tmem + 7 * NT, a0 + 7 * AS, b0 + 0 * BS, iu1, 1u);         // p = 7: plane 7
+                        }
+                        tc_commit(b_empty + 8 * st);        // frees the stage when these MMAs retire
+                    }
+                    tc_commit(b_accFull);
+                }
+            }
+        } else {
+            // ---- generator + epilogue (warps 0..7; sub-partition = warp % 4 hosts two of them) --------
+            const int kq = t & 7, cb = t >> 3;                 // k = 4 kq .. 4 kq + 3; candidates cb, cb + 32
+            const int quarter = warp & 3, half = warp >> 2;    // epilogue: TMEM lanes 32 quarter .., candidates 32 half ..
+            double z[2][DMAX + 1];
+#pragma unroll
+            for (int i = 0; i < 2; ++i) {
+                const int gj = j0 + cb + 32 * i;
+                double nrm = 0.0;
+#pragma unroll
+                for (int q = 0; q < DMAX; ++q) {
+                    const double v = (gj < M && q < kp.d) ? xnew[(size_t)gj * kp.d + q] / len_of(kp, s, q) : 0.0;
+                    z[i][q] = v;
+                    nrm += v * v;
+                }
+                z[i][DMAX] = nrm;
+            }
+            const double fx_scale = scalbn(1.0, 64 - ek);
+            double macc[2] = {0.0, 0.0};
+            double colsum[32];
+#pragma unroll
+            for (int j = 0; j < 32; ++j) colsum[j] = 0.0;
+
+            auto epilogue = [&](int rb) {
+                tc_fence_after();
+                if (!(dbg & 4)) {
+                    const int row = rb * MT + quarter * 32 + lane;
+                    const double sc = scalbn(1.0, ew[(size_t)s * n128 + row] + ek - 15);
+                    const uint32_t tl = tmem + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(half * 32);
+#pragma unroll
+                    for (int jg = 0; jg < 4; ++jg) {
+                        int32_t a[NPL][8];
+#pragma unroll
+                        for (int c = 0; c < NPL; ++c) ldtm_x8(tl + (uint32_t)(c * NT + jg * 8), a[c]);
+                        ldtm_wait();
+#pragma unroll
+                        for (int q = 0; q < 8; ++q) {
+                            double v = (double)a[NPL - 1][q];
+#pragma unroll
+                            for (int c = NPL - 2; c >= 0; --c) v = fma(v, 0.00390625, (double)a[c][q]);
+                            v *= sc;
+                            colsum[jg * 8 + q] = fma(v, v, colsum[jg * 8 + q]);
+                        }
+                    }
+                }
                 tc_fence_before();
                 __syncwarp();
                 if (lane == 0) mbar_arrive(b_accEmpty);
-                return;
-            }
-            const int row = rb * MT + quarter * 32 + lane;
-            const double sc = scalbn(1.0, ew[(size_t)s * n128 + row] + ek - 15);
-            const uint32_t tl = tmem + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(half * 32);
-#pragma unroll
-            for (int jg = 0; jg < 4; ++jg) {
-                int32_t a[NPL][8];
-#pragma unroll
-                for (int c = 0; c < NPL; ++c) ldtm_x8(tl + (uint32_t)(c * NT + jg * 8), a[c]);
-                ldtm_wait();
-#pragma unroll
-                for (int q = 0; q < 8; ++q) {
-                    double v = (double)a[NPL - 1][q];
-#pragma unroll
-                    for (int c = NPL - 2; c >= 0; --c) v = fma(v, 0.00390625, (double)a[c][q]);
-                    v *= sc;
-                    colsum[jg * 8 + q] = fma(v, v, colsum[jg * 8 + q]);
-                }
-            }
-            tc_fence_before();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(b_accEmpty);
-        };
+            };
 
-        int rb = 0, kc = 0, pending = -1, since = 0;       // pending: row block whose epilogue is deferred
-        for (int g = 0; g < NCH; ++g) {
-            const int st = g % A_STAGES, buf = g % NB;
-            mbar_wait(b_fullA + 8 * st, (g / A_STAGES) & 1);
-            double xr[4][XSP];
-            const double2 *colp = reinterpret_cast<const double2 *>(sX + (size_t)st * KC * XSP + 4 * kq);
+            const double *xs_s = xs + (size_t)s * n128 * XSP;
+            int ep = 0;                                        // next row block whose planes this warp drains
+            for (int kc = 0; kc < NKC; ++kc) {
+                double xr[4][XSP];
+                const double2 *colp = reinterpret_cast<const double2 *>(xs_s + (size_t)kc * KC * XSP + 4 * kq);
 #pragma unroll
-            for (int q = 0; q < XSP; ++q) {
-                const double2 lo2 = colp[q * (KC / 2)], hi2 = colp[q * (KC / 2) + 1];
-                xr[0][q] = lo2.x;
-                xr[1][q] = lo2.y;
-                xr[2][q] = hi2.x;
-                xr[3][q] = hi2.y;
-            }
-            double v[2][4];
-#pragma unroll
-            for (int i = 0; i < 2; ++i) {
-#pragma unroll
-                for (int r = 0; r < 4; ++r) {
-                    double xz = 0.0;
-#pragma unroll
-                    for (int q = 0; q < DMAX; ++q) xz = fma(z[i][q], xr[r][q], xz);
-                    const double r2 = (z[i][DMAX] - 2.0 * xz) + xr[r][DMAX];
-                    v[i][r] = r2 < 0.0 ? 0.0 : r2;
+                for (int q = 0; q < XSP; ++q) {
+                    const double2 lo2 = __ldg(colp + q * (KC / 2)), hi2 = __ldg(colp + q * (KC / 2) + 1);
+                    xr[0][q] = lo2.x;
+                    xr[1][q] = lo2.y;
+                    xr[2][q] = hi2.x;
+                    xr[3][q] = hi2.y;
                 }
-                if (!(dbg & 1)) k_from_r2_vec<KIND, 4>(v[i], scale);
-            }
-            if (rb == T - 1) {
+                double v[2][4];
 #pragma unroll
-                for (int i = 0; i < 2; ++i)
+                for (int i = 0; i < 2; ++i) {
+#pragma unroll
+                    for (int r = 0; r < 4; ++r) {
+                        double xz = 0.0;
+#pragma unroll
+                        for (int q = 0; q < DMAX; ++q) xz = fma(z[i][q], xr[r][q], xz);
+                        const double r2 = (z[i][DMAX] - 2.0 * xz) + xr[r][DMAX];
+                        v[i][r] = r2 < 0.0 ? 0.0 : r2;
+                    }
+                    if (!(dbg & 1)) k_from_r2_vec<KIND, 4>(v[i], scale);
 #pragma unroll
                     for (int r = 0; r < 4; ++r) macc[i] = fma(v[i][r], xr[r][DMAX + 1], macc[i]);
+                }
+                unsigned char *bt = scr + (size_t)kc * B_TILE;
+#pragma unroll
+                for (int i = 0; i < 2; ++i) {
+                    if (dbg & 8) break;
+                    uint32_t hi[4], lo[4];
+#pragma unroll
+                    for (int r = 0; r < 4; ++r) {
+                        const unsigned long long fx = __double2ull_rz(v[i][r] * fx_scale);
+                        hi[r] = (uint32_t)(fx >> 32);
+                        lo[r] = (uint32_t)fx;
+                    }
+                    const int cand = cb + 32 * i;
+#pragma unroll
+                    for (int q = 0; q < NSL; ++q) {
+                        // slice q = byte 7 - q of the fixed-point value; gather it from the 4 k values of this thread
+                        const uint32_t *w = q < 4 ? hi : lo;
+                        const uint32_t b = 3u - (uint32_t)(q & 3);
+                        const uint32_t sel = b | ((4u + b) << 4);
+                        const uint32_t p01 = __byte_perm(w[0], w[1], sel), p23 = __byte_perm(w[2], w[3], sel);
+                        *reinterpret_cast<uint32_t *>(bt + canon_off(q * NT + cand, 4 * kq, B_ROWS)) = __byte_perm(p01, p23, 0x5410);
+                    }
+                }
+                if ((kc & 3) == 3) {
+                    fence_async_all();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(b_gen + 8 * (kc >> 2));
+                }
+                // drain whatever row block has finished meanwhile (warp-uniform decision)
+                while (ep < T) {
+                    uint32_t ready = lane == 0 ? mbar_test(b_accFull, ep & 1) : 0u;
+                    ready = __shfl_sync(0xffffffffu, ready, 0);
+                    if (!ready) break;
+                    epilogue(ep++);
+                }
             }
-            mbar_wait(b_emptyB + 8 * buf, ((g / NB) & 1) ^ 1);          // MMAs of chunk g - NB have read this buffer
-            unsigned char *bt = sB + (size_t)buf * B_TILE;
+            for (; ep < T; ++ep) {
+                mbar_wait(b_accFull, ep & 1);
+                epilogue(ep);
+            }
+
+            // ---- results: column sums over the 128 lanes (= rows) of every block, means over k ----
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+                double c = colsum[j];
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+                if (lane == 0) sRed[warp * 32 + j] = c;
+            }
 #pragma unroll
             for (int i = 0; i < 2; ++i) {
-                if (dbg & 8) break;
-                uint32_t hi[4], lo[4];
-#pragma unroll
-                for (int r = 0; r < 4; ++r) {
-                    const unsigned long long fx = __double2ull_rz(v[i][r] * fx_scale);
-                    hi[r] = (uint32_t)(fx >> 32);
-                    lo[r] = (uint32_t)fx;
-                }
-                const int cand = cb + 32 * i;
-#pragma unroll
-                for (int q = 0; q < NSL; ++q) {
-                    // slice q = byte 7 - q of the fixed-point value; gather it from the 4 k values of this thread
-                    const uint32_t *w = q < 4 ? hi : lo;
-                    const uint32_t b = 3u - (uint32_t)(q & 3);
-                    const uint32_t sel = b | ((4u + b) << 4);
-                    const uint32_t p01 = __byte_perm(w[0], w[1], sel), p23 = __byte_perm(w[2], w[3], sel);
-                    *reinterpret_cast<uint32_t *>(bt + canon_off(q * NT + cand, 4 * kq, B_ROWS)) = __byte_perm(p01, p23, 0x5410);
-                }
+                double m = macc[i];
+                m += __shfl_xor_sync(0xffffffffu, m, 1);
+                m += __shfl_xor_sync(0xffffffffu, m, 2);
+                m += __shfl_xor_sync(0xffffffffu, m, 4);
+                if (kq == 0) sRed[GEN_WARPS * 32 + cb + 32 * i] = m;
             }
-            fence_async_smem();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(b_fullB + 8 * buf);
-            if (++kc == 4 * (rb + 1)) { kc = 0; pending = rb; since = 0; ++rb; }
-            else if (pending >= 0 && ++since == 2) { epilogue(pending); pending = -1; }
         }
-        if (pending >= 0) epilogue(pending);
-
-        // ---- results: column sums over the 128 lanes (= rows) of every block, means over k ----
-#pragma unroll
-        for (int j = 0; j < 32; ++j) {
-            double c = colsum[j];
-#pragma unroll
-            for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
-            if (lane == 0) sRed[warp * 32 + j] = c;
+        tc_fence_before();
+        __syncthreads();
+        if (t < NT) {
+            const int gj = j0 + t;
+            if (gj < M) {
+                const double kd = k_from_r2<KIND>(0.0, scale);
+                const double *pr = sRed + (t >> 5) * 4 * 32 + (t & 31);       // the four lane-quarter warps of this half
+                const double cs = (pr[0] + pr[32]) + (pr[64] + pr[96]);
+                if (var) var[(size_t)s * ldo + gj] = (kd + diag_add[s]) - cs;
+                if (mu) mu[(size_t)s * ldo + gj] = (m_new ? m_new[(size_t)s * ldmn + gj] : m_const) + sRed[GEN_WARPS * 32 + t];
+            }
         }
-#pragma unroll
-        for (int i = 0; i < 2; ++i) {
-            double m = macc[i];
-            m += __shfl_xor_sync(0xffffffffu, m, 1);
-            m += __shfl_xor_sync(0xffffffffu, m, 2);
-            m += __shfl_xor_sync(0xffffffffu, m, 4);
-            if (kq == 0) sRed[GEN_WARPS * 32 + cb + 32 * i] = m;
-        }
+        // the next unit's barrier re-initialisation is behind a __syncthreads: sRed is free by then
     }
     tc_fence_before();
     __syncthreads();
-    if (t < NT) {
-        const int gj = j0 + t;
-        if (gj < M) {
-            const double kd = k_from_r2<KIND>(0.0, scale);
-            const double *pr = sRed + (t >> 5) * 4 * 32 + (t & 31);       // the four lane-quarter warps of this half
-            const double cs = (pr[0] + pr[32]) + (pr[64] + pr[96]);
-            if (var) var[(size_t)s * ldo + gj] = (kd + diag_add[s]) - cs;
-            if (mu) mu[(size_t)s * ldo + gj] = (m_new ? m_new[(size_t)s * ldmn + gj] : m_const) + sRed[GEN_WARPS * 32 + t];
-        }
-    }
     if (warp == GEN_WARPS) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;\n" ::"r"(tmem) : "memory");
 }
 
@@ -459,11 +482,19 @@ predict_i8_kernel(gpx_kernel_params kp, int n, int n128, int M, const double *__
 namespace {
 struct I8Layout {
     int64_t n128, nch;
-    size_t o_xs, o_ew, o_wsl, total;
-    int64_t wsl_stride;
+    size_t o_xs, o_ew, o_wsl, o_scr, total;
+    int64_t wsl_stride, scr_stride;
+    int slots;
 };
+int i8_slots() {       // persistent CTAs = SMs of the current device, one K* slice store each
+    int dev = 0, sms = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms <= 0)
+        return 148;
+    return sms;
+}
 I8Layout i8_layout(int64_t S, int64_t n, int dmax) {
     I8Layout L;
+    L.slots = i8_slots();
     L.n128 = (n + gpx::i8::MT - 1) / gpx::i8::MT * gpx::i8::MT;
     L.nch = gpx::i8::chunks_before((int)(L.n128 / gpx::i8::MT));
     auto al = [](size_t b) { return (b + 255) / 256 * 256; };
@@ -472,6 +503,8 @@ I8Layout i8_layout(int64_t S, int64_t n, int dmax) {
     L.o_ew = o;  o += al((size_t)S * L.n128 * 4);
     L.wsl_stride = L.nch * gpx::i8::A_BLOCK;
     L.o_wsl = o; o += al((size_t)S * L.wsl_stride);
+    L.scr_stride = (L.n128 / gpx::i8::KC) * gpx::i8::B_TILE;
+    L.o_scr = o; o += al((size_t)L.slots * L.scr_stride);
     L.total = o;
     return L;
 }
@@ -497,10 +530,12 @@ int launch_i8(const gpx_kernel_params *kp, int64_t S, int64_t n, int64_t M, cons
     }
     static int dbg = -1;
     if (dbg < 0) { const char *e = getenv("GPX_I8_DEBUG"); dbg = e ? atoi(e) : 0; }
-    if (int e = ensure_smem(predict_i8_kernel<KIND, DMAX>, Cfg<DMAX>::BYTES)) return e;
-    dim3 grid((unsigned)((M + NT - 1) / NT), (unsigned)S);
-    predict_i8_kernel<KIND, DMAX><<<grid, THREADS, Cfg<DMAX>::BYTES, st>>>(
-        *kp, (int)n, (int)L.n128, (int)M, xs, xnew, wsl, L.wsl_stride, ew, m_new, m_const, diag_add, mu, var, M, M, dbg);
+    if (int e = ensure_smem(predict_i8_kernel<KIND, DMAX>, Cfg::BYTES)) return e;
+    const int64_t units = S * ((M + NT - 1) / NT);
+    const unsigned grid = (unsigned)(units < L.slots ? units : L.slots);
+    predict_i8_kernel<KIND, DMAX><<<grid, THREADS, Cfg::BYTES, st>>>(
+        *kp, (int)n, (int)L.n128, (int)M, (int)S, xs, xnew, wsl, L.wsl_stride, ew, (unsigned char *)(ws + L.o_scr), L.scr_stride,
+        m_new, m_const, diag_add, mu, var, M, M, dbg);
     count_launches(1);
     return 0;
 }
