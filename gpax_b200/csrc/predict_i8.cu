@@ -59,6 +59,9 @@ __host__ __device__ __forceinline__ int canon_off(int row, int k, int rows) {
     return (k >> 4) * (rows >> 3) * 128 + (row >> 3) * 128 + (row & 7) * 16 + (k & 15);
 }
 __host__ __device__ inline int64_t chunks_before(int rb) { return 2ll * rb * (rb + 1); }   // 4 (rb + 1) chunks per block
+// j-th chunk visited in row block rb: left to right, or boustrophedon (odd blocks right to left) so that the
+// K* chunks a block touches last are the first the next block reads (integer accumulation: any order is exact)
+__host__ __device__ __forceinline__ int walk_kc(int rb, int j, int snake) { return (snake && (rb & 1)) ? 4 * (rb + 1) - 1 - j : j; }
 
 // ---- once per factorisation: row exponents and int8 slices of W ---------------------------
 // ew[s][row] = e with |W[row][k]| * 2^-e < 1 for all k <= row (0 for an all-zero / padding row)
@@ -80,14 +83,14 @@ w_rowexp_kernel(int n, int n128, const double *__restrict__ W, int64_t ldw, int3
 // one CTA = one (row block, chunk) of one sample: 128 x 32 values -> 8 canonical byte tiles
 __global__ void __launch_bounds__(256)
 w_slice_kernel(int n, int n128, const double *__restrict__ W, int64_t ldw, const int32_t *__restrict__ ew,
-               int8_t *__restrict__ out, int64_t sample_stride) {
+               int8_t *__restrict__ out, int64_t sample_stride, int snake) {
     const int64_t s = blockIdx.y;
     // chunk id -> (rb, kc):  id = 2 rb (rb + 1) + kc
     const int id = blockIdx.x;
     int rb = (int)((sqrt(2.0 * id + 1.0) - 1.0) * 0.5);
     while (chunks_before(rb) > id) --rb;
     while (chunks_before(rb + 1) <= id) ++rb;
-    const int kc = id - (int)chunks_before(rb);
+    const int kc = walk_kc(rb, id - (int)chunks_before(rb), snake);
     int8_t *blk = out + s * sample_stride + (int64_t)id * A_BLOCK;
     for (int e = threadIdx.x; e < MT * KC; e += 256) {
         const int r = e >> 5, k = e & 31;
@@ -197,8 +200,8 @@ __device__ __forceinline__ void fence_async_all() { asm volatile("fence.proxy.as
 
 struct Cfg {
     static constexpr size_t OFF_RED = (size_t)STAGES * STAGE_BYTES;            // [8 warps][32] colsum partials + [NT] means
-    static constexpr size_t OFF_BAR = OFF_RED + (GEN_WARPS * 32 + NT) * 8;
-    static constexpr int NBAR = 2 * STAGES + MAX_T + 2;                         // full / empty per stage, gen per row block, accFull / accEmpty
+    static constexpr size_t OFF_BAR = OFF_RED + (GEN_WARPS * 32 + 2 * NT) * 8; // means: this unit's and the next one's
+    static constexpr int NBAR = 2 * STAGES + 2;                                 // full / empty per stage, accFull / accEmpty
     static constexpr size_t BYTES = OFF_BAR + NBAR * 8 + 16 + 128 /*alignment slack*/;
 };
 
@@ -210,7 +213,7 @@ predict_i8_kernel(gpx_kernel_params kp, int n, int n128, int M, int S, const dou
                   const double *__restrict__ xnew, const int8_t *__restrict__ wsl, int64_t wsl_stride,
                   const int32_t *__restrict__ ew, unsigned char *__restrict__ scratch, int64_t scratch_stride,
                   const double *__restrict__ m_new, double m_const, const double *__restrict__ diag_add,
-                  double *__restrict__ mu, double *__restrict__ var, int64_t ldo, int64_t ldmn, int dbg) {
+                  double *__restrict__ mu, double *__restrict__ var, int64_t ldo, int64_t ldmn, int snake, int dbg) {
     // dbg (GPX_I8_DEBUG, profiling only): bit 0 skips the generator arithmetic, bit 1 the MMAs,
     // bit 2 the epilogue arithmetic, bit 3 the fixed-point conversion + byte stores, bit 4 the W loads
     using C = Cfg;
@@ -221,8 +224,8 @@ predict_i8_kernel(gpx_kernel_params kp, int n, int n128, int M, int S, const dou
     uint64_t *bars = reinterpret_cast<uint64_t *>(sm + C::OFF_BAR);
     uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + C::NBAR);
     const uint32_t s_stage = smem_u32(sm);
-    const uint32_t b_full = smem_u32(bars), b_empty = b_full + 8 * STAGES, b_gen = b_empty + 8 * STAGES,
-                   b_accFull = b_gen + 8 * MAX_T, b_accEmpty = b_accFull + 8;
+    const uint32_t b_full = smem_u32(bars), b_empty = b_full + 8 * STAGES, b_accFull = b_empty + 8 * STAGES,
+                   b_accEmpty = b_accFull + 8;
 
     const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
     const int T = n128 / MT;                              // row blocks (<= MAX_T)
@@ -240,20 +243,26 @@ predict_i8_kernel(gpx_kernel_params kp, int n, int n128, int M, int S, const dou
     tc_fence_after();
     const uint32_t tmem = *tmem_slot;
 
-    for (int64_t u = blockIdx.x; u < units; u += gridDim.x) {
-        const int s = (int)(u / tiles), j0 = (int)(u % tiles) * NT;
-        const double scale = kp.scale[s];
-        const int ek = ilogb(scale) + 1;                  // 0 <= k* <= scale < 2^ek
+    // Iteration i works on unit `cur` (bulk loads, MMAs, epilogues) while the generator warps produce the
+    // K* slices of unit `nxt` into the other half of this CTA's store; iteration -1 only generates.
+    const int64_t nit = (units - (int64_t)blockIdx.x + gridDim.x - 1) / gridDim.x;
+    for (int64_t it = -1; it < nit; ++it) {
+        const bool has_cur = it >= 0, has_nxt = it + 1 < nit;
+        const int64_t ucur = (int64_t)blockIdx.x + it * gridDim.x, unxt = ucur + gridDim.x;
+        const int s = has_cur ? (int)(ucur / tiles) : 0, j0 = has_cur ? (int)(ucur % tiles) * NT : 0;
+        const unsigned char *scr_cur = scr + (size_t)(it & 1) * (size_t)(scratch_stride >> 1);
+        unsigned char *scr_nxt = scr + (size_t)((it + 1) & 1) * (size_t)(scratch_stride >> 1);
+        double *sMeanNxt = sRed + GEN_WARPS * 32 + ((it + 1) & 1) * NT;
+        const double *sMeanCur = sRed + GEN_WARPS * 32 + (it & 1) * NT;
         // every barrier starts the unit in phase 0 (all of them are quiescent here: the last epilogue
         // waited for the last commit, which follows every earlier arrival)
-        if (t == 0) {
-            if (u != (int64_t)blockIdx.x)
+        if (t == 0 && has_cur) {
+            if (it > 0)
                 for (int i = 0; i < C::NBAR; ++i) mbar_inval(b_full + 8 * i);
             for (int i = 0; i < STAGES; ++i) {
                 mbar_init(b_full + 8 * i, 1);
                 mbar_init(b_empty + 8 * i, 1);
             }
-            for (int i = 0; i < MAX_T; ++i) mbar_init(b_gen + 8 * i, GEN_WARPS);
             mbar_init(b_accFull, 1);
             mbar_init(b_accEmpty, GEN_WARPS);
             asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
@@ -263,24 +272,25 @@ predict_i8_kernel(gpx_kernel_params kp, int n, int n128, int M, int S, const dou
 
         if (warp == GEN_WARPS + 1) {
             // ---- producer thread: per chunk one W slice block (stored in walk order) + the chunk's K* slices
-            if (lane == 0) {
+            if (lane == 0 && has_cur) {
                 const int8_t *src = wsl + (int64_t)s * wsl_stride;
                 int g = 0;
                 for (int rb = 0; rb < T; ++rb) {
-                    mbar_wait(b_gen + 8 * rb, 0);                              // K* chunks 0 .. 4 rb + 3 are in the store
-                    for (int kc = 0; kc < 4 * (rb + 1); ++kc, ++g) {
+                    const int nk = 4 * (rb + 1);
+                    for (int j = 0; j < nk; ++j, ++g) {
+                        const int kc = walk_kc(rb, j, snake);
                         const int st = g % STAGES;
                         mbar_wait(b_empty + 8 * st, ((g / STAGES) & 1) ^ 1);   // MMAs of chunk g - STAGES retired
                         mbar_arrive_expect_tx(b_full + 8 * st, ((dbg & 16) ? 0 : A_BLOCK) + B_TILE);
                         const uint32_t dst = s_stage + (uint32_t)st * STAGE_BYTES;
                         if (!(dbg & 16)) bulk_load(dst, src + (int64_t)g * A_BLOCK, A_BLOCK, b_full + 8 * st);
-                        bulk_load(dst + A_BLOCK, scr + (size_t)kc * B_TILE, B_TILE, b_full + 8 * st);
+                        bulk_load(dst + A_BLOCK, scr_cur + (size_t)kc * B_TILE, B_TILE, b_full + 8 * st);
                     }
                 }
             }
         } else if (warp == GEN_WARPS) {
             // ---- MMA issuer: 12 UTCIMMA per chunk, every descriptor one add away from a per-chunk base
-            if (lane == 0) {
+            if (lane == 0 && has_cur) {
                 const uint64_t descA0 = make_desc(s_stage, (MT / 8) * 128, 128);
                 const uint64_t descB0 = make_desc(s_stage + A_BLOCK, (B_ROWS / 8) * 128, 128);
                 const uint32_t iu1 = make_idesc(NT * 1, false), iu2 = make_idesc(NT * 2, false), iu3 = make_idesc(NT * 3, false),
@@ -288,17 +298,17 @@ predict_i8_kernel(gpx_kernel_params kp, int n, int n128, int M, int S, const dou
                 int g = 0;
                 for (int rb = 0; rb < T; ++rb) {
                     if (rb > 0) {
-                        mbar_wait(b_accEmpty, (rb - 1) & 1);       // the epilogue has drained the planes
+                        mbar_wait(b_accEmpty, (rb - 1) & 1);       // the epilogue has the planes in registers
                         tc_fence_after();
                     }
-                    for (int kc = 0; kc < 4 * (rb + 1); ++kc, ++g) {
+                    for (int j = 0; j < 4 * (rb + 1); ++j, ++g) {
                         const int st = g % STAGES;
                         mbar_wait(b_full + 8 * st, (g / STAGES) & 1);
                         tc_fence_after();
                         if (!(dbg & 2)) {
                             const uint64_t a0 = descA0 + (uint64_t)(st * (STAGE_BYTES >> 4));
                             const uint64_t b0 = descB0 + (uint64_t)(st * (STAGE_BYTES >> 4));
-                            const uint32_t acc0 = kc > 0 ? 1u : 0u;
+                            const uint32_t acc0 = j > 0 ? 1u : 0u;
                             constexpr uint64_t AS = A_TILE >> 4, BS = ((NT / 8) * 128) >> 4;     // descriptor steps per slice
                             // W slice p (byte 7 - p; the top one signed) x stacked K* slices q0.. -> planes p + q0..
                             mma_i8(tmem + 0 * NT, a0 + 0 * AS, b0 + 0 * BS, is4, acc0);       // p = 0: planes 0..3
@@ -320,153 +330,164 @@ predict_i8_kernel(gpx_kernel_params kp, int n, int n128, int M, int S, const dou
                 }
             }
         } else {
-            // ---- generator + epilogue (warps 0..7; sub-partition = warp % 4 hosts two of them) --------
+            // ---- generator (unit nxt) + epilogue (unit cur): warps 0..7, two per SM sub-partition --------
             const int kq = t & 7, cb = t >> 3;                 // k = 4 kq .. 4 kq + 3; candidates cb, cb + 32
             const int quarter = warp & 3, half = warp >> 2;    // epilogue: TMEM lanes 32 quarter .., candidates 32 half ..
-            double z[2][DMAX + 1];
-#pragma unroll
-            for (int i = 0; i < 2; ++i) {
-                const int gj = j0 + cb + 32 * i;
-                double nrm = 0.0;
-#pragma unroll
-                for (int q = 0; q < DMAX; ++q) {
-                    const double v = (gj < M && q < kp.d) ? xnew[(size_t)gj * kp.d + q] / len_of(kp, s, q) : 0.0;
-                    z[i][q] = v;
-                    nrm += v * v;
-                }
-                z[i][DMAX] = nrm;
-            }
-            const double fx_scale = scalbn(1.0, 64 - ek);
-            double macc[2] = {0.0, 0.0};
+            const int ekc = has_cur ? ilogb(kp.scale[s]) + 1 : 0;
             double colsum[32];
 #pragma unroll
             for (int j = 0; j < 32; ++j) colsum[j] = 0.0;
 
             auto epilogue = [&](int rb) {
                 tc_fence_after();
-                if (!(dbg & 4)) {
-                    const int row = rb * MT + quarter * 32 + lane;
-                    const double sc = scalbn(1.0, ew[(size_t)s * n128 + row] + ek - 15);
-                    const uint32_t tl = tmem + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(half * 32);
+                const int row = rb * MT + quarter * 32 + lane;
+                // value = (X0 + X1 2^-24 + X2 2^-48) 2^(e_row + e_K - 15 - 16), X = three planes merged exactly in int64
+                const double sc = scalbn(1.0, ew[(size_t)s * n128 + row] + ekc - 31);
+                const uint32_t tl = tmem + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(half * 32);
 #pragma unroll
-                    for (int jg = 0; jg < 4; ++jg) {
-                        int32_t a[NPL][8];
+                for (int jg = 0; jg < 4; ++jg) {
+                    int32_t a[NPL][8];
 #pragma unroll
-                        for (int c = 0; c < NPL; ++c) ldtm_x8(tl + (uint32_t)(c * NT + jg * 8), a[c]);
-                        ldtm_wait();
+                    for (int c = 0; c < NPL; ++c) ldtm_x8(tl + (uint32_t)(c * NT + jg * 8), a[c]);
+                    ldtm_wait();
+                    if (jg == 3) {                             // the planes are in registers: the next row block may start
+                        tc_fence_before();
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive(b_accEmpty);
+                    }
+                    if (dbg & 4) continue;
 #pragma unroll
-                        for (int q = 0; q < 8; ++q) {
-                            double v = (double)a[NPL - 1][q];
-#pragma unroll
-                            for (int c = NPL - 2; c >= 0; --c) v = fma(v, 0.00390625, (double)a[c][q]);
-                            v *= sc;
-                            colsum[jg * 8 + q] = fma(v, v, colsum[jg * 8 + q]);
-                        }
+                    for (int q = 0; q < 8; ++q) {
+                        const long long X0 = ((long long)a[0][q] << 16) + ((long long)a[1][q] << 8) + (long long)a[2][q];
+                        const long long X1 = ((long long)a[3][q] << 16) + ((long long)a[4][q] << 8) + (long long)a[5][q];
+                        const long long X2 = ((long long)a[6][q] << 16) + ((long long)a[7][q] << 8);
+                        // |X| < 2^48: int64 -> double through the 2^52 + 2^51 bias (one integer add, one DADD)
+                        const double d0 = __longlong_as_double(X0 + 0x4338000000000000LL) - 6755399441055744.0;
+                        const double d1 = __longlong_as_double(X1 + 0x4338000000000000LL) - 6755399441055744.0;
+                        const double d2 = __longlong_as_double(X2 + 0x4338000000000000LL) - 6755399441055744.0;
+                        const double v = fma(fma(d2, 5.9604644775390625e-08, d1), 5.9604644775390625e-08, d0) * sc;
+                        colsum[jg * 8 + q] = fma(v, v, colsum[jg * 8 + q]);
                     }
                 }
-                tc_fence_before();
-                __syncwarp();
-                if (lane == 0) mbar_arrive(b_accEmpty);
             };
-
-            const double *xs_s = xs + (size_t)s * n128 * XSP;
-            int ep = 0;                                        // next row block whose planes this warp drains
-            for (int kc = 0; kc < NKC; ++kc) {
-                double xr[4][XSP];
-                const double2 *colp = reinterpret_cast<const double2 *>(xs_s + (size_t)kc * KC * XSP + 4 * kq);
-#pragma unroll
-                for (int q = 0; q < XSP; ++q) {
-                    const double2 lo2 = __ldg(colp + q * (KC / 2)), hi2 = __ldg(colp + q * (KC / 2) + 1);
-                    xr[0][q] = lo2.x;
-                    xr[1][q] = lo2.y;
-                    xr[2][q] = hi2.x;
-                    xr[3][q] = hi2.y;
-                }
-                double v[2][4];
-#pragma unroll
-                for (int i = 0; i < 2; ++i) {
-#pragma unroll
-                    for (int r = 0; r < 4; ++r) {
-                        double xz = 0.0;
-#pragma unroll
-                        for (int q = 0; q < DMAX; ++q) xz = fma(z[i][q], xr[r][q], xz);
-                        const double r2 = (z[i][DMAX] - 2.0 * xz) + xr[r][DMAX];
-                        v[i][r] = r2 < 0.0 ? 0.0 : r2;
-                    }
-                    if (!(dbg & 1)) k_from_r2_vec<KIND, 4>(v[i], scale);
-#pragma unroll
-                    for (int r = 0; r < 4; ++r) macc[i] = fma(v[i][r], xr[r][DMAX + 1], macc[i]);
-                }
-                unsigned char *bt = scr + (size_t)kc * B_TILE;
-#pragma unroll
-                for (int i = 0; i < 2; ++i) {
-                    if (dbg & 8) break;
-                    uint32_t hi[4], lo[4];
-#pragma unroll
-                    for (int r = 0; r < 4; ++r) {
-                        const unsigned long long fx = __double2ull_rz(v[i][r] * fx_scale);
-                        hi[r] = (uint32_t)(fx >> 32);
-                        lo[r] = (uint32_t)fx;
-                    }
-                    const int cand = cb + 32 * i;
-#pragma unroll
-                    for (int q = 0; q < NSL; ++q) {
-                        // slice q = byte 7 - q of the fixed-point value; gather it from the 4 k values of this thread
-                        const uint32_t *w = q < 4 ? hi : lo;
-                        const uint32_t b = 3u - (uint32_t)(q & 3);
-                        const uint32_t sel = b | ((4u + b) << 4);
-                        const uint32_t p01 = __byte_perm(w[0], w[1], sel), p23 = __byte_perm(w[2], w[3], sel);
-                        *reinterpret_cast<uint32_t *>(bt + canon_off(q * NT + cand, 4 * kq, B_ROWS)) = __byte_perm(p01, p23, 0x5410);
-                    }
-                }
-                if ((kc & 3) == 3) {
-                    fence_async_all();
-                    __syncwarp();
-                    if (lane == 0) mbar_arrive(b_gen + 8 * (kc >> 2));
-                }
-                // drain whatever row block has finished meanwhile (warp-uniform decision)
+            int ep = has_cur ? 0 : T;                          // next row block whose planes this warp drains
+            auto poll = [&]() {
                 while (ep < T) {
                     uint32_t ready = lane == 0 ? mbar_test(b_accFull, ep & 1) : 0u;
                     ready = __shfl_sync(0xffffffffu, ready, 0);
                     if (!ready) break;
                     epilogue(ep++);
                 }
+            };
+
+            if (has_nxt) {
+                const int sn = (int)(unxt / tiles), jn = (int)(unxt % tiles) * NT;
+                const double scale = kp.scale[sn];
+                const int ek = ilogb(scale) + 1;               // 0 <= k* <= scale < 2^ek
+                double z[2][DMAX + 1];
+#pragma unroll
+                for (int i = 0; i < 2; ++i) {
+                    const int gj = jn + cb + 32 * i;
+                    double nrm = 0.0;
+#pragma unroll
+                    for (int q = 0; q < DMAX; ++q) {
+                        const double v = (gj < M && q < kp.d) ? xnew[(size_t)gj * kp.d + q] / len_of(kp, sn, q) : 0.0;
+                        z[i][q] = v;
+                        nrm += v * v;
+                    }
+                    z[i][DMAX] = nrm;
+                }
+                const double fx_scale = scalbn(1.0, 64 - ek);
+                double macc[2] = {0.0, 0.0};
+                const double *xs_s = xs + (size_t)sn * n128 * XSP;
+                for (int kc = 0; kc < NKC; ++kc) {
+                    double xr[4][XSP];
+                    const double2 *colp = reinterpret_cast<const double2 *>(xs_s + (size_t)kc * KC * XSP + 4 * kq);
+#pragma unroll
+                    for (int q = 0; q < XSP; ++q) {
+                        const double2 lo2 = __ldg(colp + q * (KC / 2)), hi2 = __ldg(colp + q * (KC / 2) + 1);
+                        xr[0][q] = lo2.x;
+                        xr[1][q] = lo2.y;
+                        xr[2][q] = hi2.x;
+                        xr[3][q] = hi2.y;
+                    }
+                    double v[2][4];
+#pragma unroll
+                    for (int i = 0; i < 2; ++i) {
+#pragma unroll
+                        for (int r = 0; r < 4; ++r) {
+                            double xz = 0.0;
+#pragma unroll
+                            for (int q = 0; q < DMAX; ++q) xz = fma(z[i][q], xr[r][q], xz);
+                            const double r2 = (z[i][DMAX] - 2.0 * xz) + xr[r][DMAX];
+                            v[i][r] = r2 < 0.0 ? 0.0 : r2;
+                        }
+                        if (!(dbg & 1)) k_from_r2_vec<KIND, 4>(v[i], scale);
+#pragma unroll
+                        for (int r = 0; r < 4; ++r) macc[i] = fma(v[i][r], xr[r][DMAX + 1], macc[i]);
+                    }
+                    unsigned char *bt = scr_nxt + (size_t)kc * B_TILE;
+#pragma unroll
+                    for (int i = 0; i < 2; ++i) {
+                        if (dbg & 8) break;
+                        uint32_t hi[4], lo[4];
+#pragma unroll
+                        for (int r = 0; r < 4; ++r) {
+                            const unsigned long long fx = __double2ull_rz(v[i][r] * fx_scale);
+                            hi[r] = (uint32_t)(fx >> 32);
+                            lo[r] = (uint32_t)fx;
+                        }
+                        const int cand = cb + 32 * i;
+#pragma unroll
+                        for (int q = 0; q < NSL; ++q) {
+                            // slice q = byte 7 - q of the fixed-point value; gather it from the 4 k values of this thread
+                            const uint32_t *w = q < 4 ? hi : lo;
+                            const uint32_t b = 3u - (uint32_t)(q & 3);
+                            const uint32_t sel = b | ((4u + b) << 4);
+                            const uint32_t p01 = __byte_perm(w[0], w[1], sel), p23 = __byte_perm(w[2], w[3], sel);
+                            *reinterpret_cast<uint32_t *>(bt + canon_off(q * NT + cand, 4 * kq, B_ROWS)) = __byte_perm(p01, p23, 0x5410);
+                        }
+                    }
+                    poll();                                    // drain whatever row block of `cur` has finished meanwhile
+                }
+                fence_async_all();                             // the store is read by bulk copies after the next __syncthreads
+#pragma unroll
+                for (int i = 0; i < 2; ++i) {
+                    double m = macc[i];
+                    m += __shfl_xor_sync(0xffffffffu, m, 1);
+                    m += __shfl_xor_sync(0xffffffffu, m, 2);
+                    m += __shfl_xor_sync(0xffffffffu, m, 4);
+                    if (kq == 0) sMeanNxt[cb + 32 * i] = m;
+                }
             }
             for (; ep < T; ++ep) {
                 mbar_wait(b_accFull, ep & 1);
                 epilogue(ep);
             }
-
-            // ---- results: column sums over the 128 lanes (= rows) of every block, means over k ----
+            if (has_cur) {
+                // column sums over the 128 lanes (= rows) of every block
 #pragma unroll
-            for (int j = 0; j < 32; ++j) {
-                double c = colsum[j];
+                for (int j = 0; j < 32; ++j) {
+                    double c = colsum[j];
 #pragma unroll
-                for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
-                if (lane == 0) sRed[warp * 32 + j] = c;
-            }
-#pragma unroll
-            for (int i = 0; i < 2; ++i) {
-                double m = macc[i];
-                m += __shfl_xor_sync(0xffffffffu, m, 1);
-                m += __shfl_xor_sync(0xffffffffu, m, 2);
-                m += __shfl_xor_sync(0xffffffffu, m, 4);
-                if (kq == 0) sRed[GEN_WARPS * 32 + cb + 32 * i] = m;
+                    for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+                    if (lane == 0) sRed[warp * 32 + j] = c;
+                }
             }
         }
         tc_fence_before();
         __syncthreads();
-        if (t < NT) {
+        if (t < NT && has_cur) {
             const int gj = j0 + t;
             if (gj < M) {
-                const double kd = k_from_r2<KIND>(0.0, scale);
+                const double kd = k_from_r2<KIND>(0.0, kp.scale[s]);
                 const double *pr = sRed + (t >> 5) * 4 * 32 + (t & 31);       // the four lane-quarter warps of this half
                 const double cs = (pr[0] + pr[32]) + (pr[64] + pr[96]);
                 if (var) var[(size_t)s * ldo + gj] = (kd + diag_add[s]) - cs;
-                if (mu) mu[(size_t)s * ldo + gj] = (m_new ? m_new[(size_t)s * ldmn + gj] : m_const) + sRed[GEN_WARPS * 32 + t];
+                if (mu) mu[(size_t)s * ldo + gj] = (m_new ? m_new[(size_t)s * ldmn + gj] : m_const) + sMeanCur[t];
             }
         }
-        // the next unit's barrier re-initialisation is behind a __syncthreads: sRed is free by then
+        // the next iteration starts with a __syncthreads: sRed is free by the time it is written again
     }
     tc_fence_before();
     __syncthreads();
@@ -503,7 +524,7 @@ I8Layout i8_layout(int64_t S, int64_t n, int dmax) {
     L.o_ew = o;  o += al((size_t)S * L.n128 * 4);
     L.wsl_stride = L.nch * gpx::i8::A_BLOCK;
     L.o_wsl = o; o += al((size_t)S * L.wsl_stride);
-    L.scr_stride = (L.n128 / gpx::i8::KC) * gpx::i8::B_TILE;
+    L.scr_stride = 2 * (L.n128 / gpx::i8::KC) * gpx::i8::B_TILE;      // this unit's slices and the next one's
     L.o_scr = o; o += al((size_t)L.slots * L.scr_stride);
     L.total = o;
     return L;
@@ -522,10 +543,12 @@ int launch_i8(const gpx_kernel_params *kp, int64_t S, int64_t n, int64_t M, cons
     double *xs = (double *)(ws + L.o_xs);
     int32_t *ew = (int32_t *)(ws + L.o_ew);
     int8_t *wsl = (int8_t *)(ws + L.o_wsl);
+    static int snake = -1;
+    if (snake < 0) { const char *e = getenv("GPX_I8_SNAKE"); snake = e ? atoi(e) : 1; }
     if (prepare) {
         xs_prep_kernel<DMAX><<<dim3((unsigned)((L.n128 + 255) / 256), (unsigned)S), 256, 0, st>>>(*kp, (int)n, (int)L.n128, x, alpha, xs);
         w_rowexp_kernel<<<dim3((unsigned)(L.n128 / 8), (unsigned)S), 256, 0, st>>>((int)n, (int)L.n128, W, ldw, ew);
-        w_slice_kernel<<<dim3((unsigned)L.nch, (unsigned)S), 256, 0, st>>>((int)n, (int)L.n128, W, ldw, ew, wsl, L.wsl_stride);
+        w_slice_kernel<<<dim3((unsigned)L.nch, (unsigned)S), 256, 0, st>>>((int)n, (int)L.n128, W, ldw, ew, wsl, L.wsl_stride, snake);
         count_launches(3);
     }
     static int dbg = -1;
@@ -535,7 +558,7 @@ int launch_i8(const gpx_kernel_params *kp, int64_t S, int64_t n, int64_t M, cons
     const unsigned grid = (unsigned)(units < L.slots ? units : L.slots);
     predict_i8_kernel<KIND, DMAX><<<grid, THREADS, Cfg::BYTES, st>>>(
         *kp, (int)n, (int)L.n128, (int)M, (int)S, xs, xnew, wsl, L.wsl_stride, ew, (unsigned char *)(ws + L.o_scr), L.scr_stride,
-        m_new, m_const, diag_add, mu, var, M, M, dbg);
+        m_new, m_const, diag_add, mu, var, M, M, snake, dbg);
     count_launches(1);
     return 0;
 }
