@@ -229,6 +229,46 @@ class Clocks:
 # ---------------------------------------------------------------------------
 # our arm
 # ---------------------------------------------------------------------------
+def measured_peaks():
+    """The driver-written MEASURED_PEAKS.json next to this file, or None."""
+    try:
+        with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "MEASURED_PEAKS.json")) as f:
+            return json.load(f)
+    except Exception:
+        return None
+
+
+def measure_int8_peak(torch, dev):
+    """Self-measured INT8 tensor-core roofline denominator for the Ozaki route (MEASURED_PEAKS.json
+    has bf16 only): cuBLASLt int8 x int8 -> int32 GEMM 8192 x 8192 x 16384 through torch._int_mm,
+    sustained over ~1 s, CUDA events.  None when the library call is unavailable (the caller then
+    falls back to the UTCIMMA probe figure in profiles/r02/tcgen05_i8_probe.jsonl)."""
+    try:
+        Mm, Kk, Nn = 8192, 16384, 8192
+        a = torch.randint(-127, 127, (Mm, Kk), dtype=torch.int8, device=dev)
+        b = torch.randint(-127, 127, (Kk, Nn), dtype=torch.int8, device=dev)
+        for _ in range(3):
+            torch._int_mm(a, b)
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(True), torch.cuda.Event(True)
+        e0.record()
+        torch._int_mm(a, b)
+        e1.record()
+        torch.cuda.synchronize()
+        reps = max(3, int(1000 / max(e0.elapsed_time(e1), 1e-3)))
+        e0.record()
+        for _ in range(reps):
+            torch._int_mm(a, b)
+        e1.record()
+        torch.cuda.synchronize()
+        tops = 2.0 * Mm * Kk * Nn * reps / (e0.elapsed_time(e1) * 1e-3) / 1e12
+        del a, b
+        torch.cuda.empty_cache()
+        return tops
+    except Exception:
+        return None
+
+
 def measure_dgemm_peak(torch, dev):
     """Self-measured FP64 roofline denominator (MEASURED_PEAKS.json has no FP64
     entry): cuBLAS DGEMM 8192^3, best of 5 (burst) and a 2 s loop
@@ -327,6 +367,7 @@ def run_ours(args):
         xbuf = (torch.empty(world * S_local * my_cnt, dtype=torch.float64, device=dev),
                 torch.empty(world * S_local * my_cnt, dtype=torch.float64, device=dev))
     pws = E.predict_ws_alloc(S_local, n, d, dev)
+    m_blk = min(c for _, _, c in layout if c)     # the smallest block decides the route for all of them
     peer, exchange = None, "none (1 rank)"
     if world > 1:
         exchange = "nccl all_to_all_single"
@@ -356,18 +397,21 @@ def run_ours(args):
         E.trtri(bufL, n, dinv, bufW)
         if timed_events is not None:
             timed_events["pred0"].record()
+        # one INT8-route attachment for all blocks of the step: W is sliced once (engine.i8_session)
         if peer is not None:
             peer.begin()
-            for co, cnt, mu_r, var_r in peer.targets:      # block r goes straight into rank r's HBM
-                if cnt:
-                    E.predict(hpd, di["x"], di["x_new"][co:co + cnt], bufW, alpha, hpd.jitter, None, 1.0, True,
-                              True, mu_r, var_r, pws)
+            with E.i8_session(hpd, n, m_blk, dev):
+                for co, cnt, mu_r, var_r in peer.targets:      # block r goes straight into rank r's HBM
+                    if cnt:
+                        E.predict(hpd, di["x"], di["x_new"][co:co + cnt], bufW, alpha, hpd.jitter, None, 1.0,
+                                  True, True, mu_r, var_r, pws)
         else:
-            for eo, co, cnt in layout:             # one block per reducing rank (one block at N = 1)
-                if cnt:
-                    E.predict(hpd, di["x"], di["x_new"][co:co + cnt], bufW, alpha, hpd.jitter, None, 1.0, True,
-                              True, mu[eo:eo + S_local * cnt].view(S_local, cnt),
-                              var[eo:eo + S_local * cnt].view(S_local, cnt), pws)
+            with E.i8_session(hpd, n, m_blk, dev):
+                for eo, co, cnt in layout:             # one block per reducing rank (one block at N = 1)
+                    if cnt:
+                        E.predict(hpd, di["x"], di["x_new"][co:co + cnt], bufW, alpha, hpd.jitter, None, 1.0,
+                                  True, True, mu[eo:eo + S_local * cnt].view(S_local, cnt),
+                                  var[eo:eo + S_local * cnt].view(S_local, cnt), pws)
         if timed_events is not None:
             timed_events["pred1"].record()
         # every candidate is reduced over ALL samples on one rank, in global sample order
@@ -391,8 +435,10 @@ def run_ours(args):
 
     # FP64 roofline denominator, measured on this GPU before the timed region
     dgemm_burst, dgemm_sustained = (None, None)
+    int8_peak = None
     if rank == 0:
         dgemm_burst, dgemm_sustained = measure_dgemm_peak(torch, dev)
+        int8_peak = measure_int8_peak(torch, dev)
 
     for _ in range(args.warmup):
         one_step(dev_inputs)
@@ -466,7 +512,36 @@ def run_ours(args):
         chol_tflops = S_local * n**3 / 3.0 / (t_chol * 1e-3) / 1e12
         achieved = pred_flops / (t_pred * 1e-3) / 1e12
         peak = dgemm_sustained
-        traffic, traffic_src = ncu_traffic("predict_ws_kernel", S_local, n, M)
+        solver = E.predict_solver(_hpd_from_device(E, wl.kind, d, dev_inputs, dev), n, m_blk)
+        traffic, traffic_src = ncu_traffic("predict_i8_kernel" if solver == "int8-ozaki" else "predict_ws_kernel",
+                                           S_local, n, M)
+        if solver == "int8-ozaki":
+            # 36 int8 slice products per fp64 multiply-add; peak = cuBLASLt int8 GEMM measured in this run
+            i8_ops = 36.0 * pred_flops / (t_pred * 1e-3) / 1e12
+            mp = measured_peaks()
+            bf16_sus = (mp or {}).get("bf16_tflops_sustained")
+            i8_peak = 2.0 * bf16_sus if bf16_sus else 3825.0
+            roof = {"kernel": "predict_i8_kernel (W K*^T emulated exactly on tcgen05.mma kind::i8: 8 byte slices per "
+                              "operand, 36 slice products, INT32 planes in TMEM; + the one-off slicing of W)",
+                    "bound": "tensor", "achieved": i8_ops, "peak": i8_peak, "unit": "TOP/s (int8)",
+                    "frac": i8_ops / i8_peak, "traffic": traffic, "traffic_source": traffic_src,
+                    "peak_source": ("2 x bf16_tflops_sustained of MEASURED_PEAKS.json (the kernel is timed inside a long, "
+                                    "power-capped step; dense int8 = 2 x dense bf16 on this part; the file has no int8 entry)"
+                                    if bf16_sus else
+                                    "UTCIMMA M128 N256 K32 burst probe, profiles/r02/tcgen05_i8_probe.jsonl "
+                                    "(MEASURED_PEAKS.json absent)"),
+                    "cublaslt_int8_tops_this_run": int8_peak, "utcimma_burst_probe_tops": 3825.1,
+                    "fp64_equivalent_tflops": achieved, "dgemm_peak_tflops": peak,
+                    "fp64_equivalent_vs_dgemm_peak": achieved / peak if peak else None,
+                    "ms_per_launch": t_pred, "launches_per_step": sum(1 for _, _, c in layout if c)}
+        else:
+            roof = {"kernel": "predict_ws_kernel (fused K* generation + TMA-fed W*K*^T on DMMA + column norms)",
+                    "bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
+                    "frac": achieved / peak if peak else None,
+                    "traffic": traffic, "traffic_source": traffic_src,
+                    "peak_source": "self-measured cuBLAS DGEMM 8192^3 sustained on this GPU in this run "
+                                   "(MEASURED_PEAKS.json has no FP64 entry); burst = %.1f" % dgemm_burst,
+                    "ms_per_launch": t_pred, "launches_per_step": sum(1 for _, _, c in layout if c)}
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": per_step, "higher_is_better": True,
@@ -476,13 +551,8 @@ def run_ours(args):
                     "d2h_bytes_per_step": d2h_bytes},
             "gpu_launches": int(launches),
             "clocks": clk.summary(),
-            "roofline": {"kernel": "predict_ws_kernel (fused K* generation + TMA-fed W*K*^T on DMMA + column norms)",
-                         "bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
-                         "frac": achieved / peak if peak else None,
-                         "traffic": traffic, "traffic_source": traffic_src,
-                         "peak_source": "self-measured cuBLAS DGEMM 8192^3 sustained on this GPU in this run "
-                                        "(MEASURED_PEAKS.json has no FP64 entry); burst = %.1f" % dgemm_burst,
-                         "ms_per_launch": t_pred, "launches_per_step": sum(1 for _, _, c in layout if c)},
+            "roofline": roof,
+            "predict_solver": solver,
             "cholesky": {"tflops": chol_tflops, "ms": t_chol,
                          "frac_of_dgemm": chol_tflops / peak if peak else None,
                          "flops": "S*n^3/3", "peak": "self-measured cuBLAS DGEMM (as roofline.peak_source)"},

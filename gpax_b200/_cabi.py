@@ -65,6 +65,8 @@ SIGNATURES = {
     "gpx_predict_i8_ws_bytes": (_sz, [_i64, _i64, _i32]),
     "gpx_predict_i8": (C.c_int, [_kp, _i64, _i64, _i64, _ptr, _ptr, _ptr, _i64, _ptr, _ptr, _dbl,
                                  _ptr, _ptr, _ptr, _i32, _ptr, _ptr]),
+    "gpx_predict_i8_want": (_sz, [_kp, _i64, _i64, _i64]),
+    "gpx_predict_i8_attach": (None, [_ptr, _sz, _i32]),
     "gpx_predict_static": (C.c_int, [_kp, _i64, _i64, _i64, _ptr, _ptr, _ptr, _i64, _ptr, _ptr, _dbl,
                                      _ptr, _ptr, _ptr, _ptr]),
     "gpx_acq_parts": (_i64, [_i64]),
@@ -90,7 +92,7 @@ for _name, (_res, _args) in SIGNATURES.items():
     _fn.restype = _res
     _fn.argtypes = _args
 
-ABI_VERSION = 9
+ABI_VERSION = 10
 if lib.gpx_abi_version() != ABI_VERSION:
     raise ImportError("libgpax_b200.so ABI version mismatch")
 

@@ -789,14 +789,67 @@ extern "C" size_t gpx_predict_ws_bytes(int64_t S, int64_t n, int32_t d) {
     return (size_t)S * n_pad * (size_t)(dm + 2) * sizeof(double);
 }
 
+// ---- INT8 tensor-core route (predict_i8.cu) ------------------------------------------------
+// gpx_predict / gpx_predict_acq keep their signatures: a caller that wants the faster route attaches
+// a workspace of gpx_predict_i8_want(...) bytes to its host thread; supported shapes then go through
+// predict_i8_core, everything else (and every call without an attachment) through the FP64 DMMA kernels.
+namespace gpx {
+int predict_i8_supported(const gpx_kernel_params *kp, int64_t n);
+int predict_i8_core(const gpx_kernel_params *kp, int64_t S, int64_t n, int64_t M, const double *x,
+                    const double *xnew, const double *W, int64_t ldw, const double *alpha,
+                    const double *m_new, double m_const, const double *diag_add, double *mu, double *var,
+                    int64_t ldo, int64_t ldmn, int prepare, void *ws, cudaStream_t st);
+}
+namespace {
+thread_local void *tl_i8_ws = nullptr;
+thread_local size_t tl_i8_bytes = 0;
+thread_local bool tl_i8_keep = false;              // the attachment spans several calls against one factorisation
+struct I8Key { const void *W; int64_t S, n; };
+thread_local I8Key tl_i8_prepared = {nullptr, 0, 0};
+}
+extern "C" size_t gpx_predict_i8_ws_bytes(int64_t S, int64_t n, int32_t d);
+
+extern "C" size_t gpx_predict_i8_want(const gpx_kernel_params *kp, int64_t S, int64_t n, int64_t M) {
+    // GPX_PREDICT_I8=0 switches the route off.  Below 512 candidates the one-off slicing of W
+    // (reads 8 n^2, writes 4 n^2 bytes per sample) is not amortised.
+    static int enabled = -1;
+    if (enabled < 0) { const char *e = getenv("GPX_PREDICT_I8"); enabled = (e && atoi(e) == 0) ? 0 : 1; }
+    if (!enabled || !kp || gpx::validate_kp(kp) != 0 || S <= 0 || M < 512) return 0;
+    if (!gpx::predict_i8_supported(kp, n)) return 0;
+    return gpx_predict_i8_ws_bytes(S, n, kp->d);
+}
+
+extern "C" void gpx_predict_i8_attach(void *ws, size_t bytes, int32_t same_factorisation) {
+    tl_i8_ws = ws;
+    tl_i8_bytes = ws ? bytes : 0;
+    tl_i8_keep = ws && same_factorisation;
+    tl_i8_prepared = {nullptr, 0, 0};
+}
+
+// the attached workspace serves this call (decided once per call, on the whole candidate count)
+static bool predict_route_i8(const gpx_kernel_params *kp, int64_t S, int64_t n, int64_t M) {
+    if (!tl_i8_ws) return false;
+    const size_t want = gpx_predict_i8_want(kp, S, n, M);
+    return want > 0 && want <= tl_i8_bytes;
+}
+
 // strided core shared by gpx_predict (ldo = ldmn = M) and the candidate-tiled gpx_predict_acq
 static int predict_core(const gpx_kernel_params *kp, int64_t S, int64_t n, int64_t M,
                         const double *x, const double *xnew, const double *W, int64_t ldw,
                         const double *alpha, const double *m_new, double m_const,
                         const double *diag_add, double *mu, double *var, int64_t ldo, int64_t ldmn,
-                        bool prep, void *ws, cudaStream_t st) {
+                        bool prep, void *ws, cudaStream_t st, bool i8 = false) {
     using namespace gpx;
     int rc;
+    if (i8) {
+        const bool have = tl_i8_keep && tl_i8_prepared.W == (const void *)W && tl_i8_prepared.S == S && tl_i8_prepared.n == n;
+        rc = predict_i8_core(kp, S, n, M, x, xnew, W, ldw, alpha, m_new, m_const, diag_add, mu, var, ldo, ldmn,
+                             (prep && !have) ? 1 : 0, tl_i8_ws, st);
+        if (rc) return rc;
+        tl_i8_prepared = {W, S, n};
+        GPX_LAUNCH_CHECK();
+        return 0;
+    }
     switch (kp->kind) {
         case GPX_RBF:
             rc = dispatch_predict<GPX_RBF>(kp, S, n, M, x, xnew, W, ldw, alpha, m_new, m_const, diag_add, mu, var, ldo, ldmn, prep, (double *)ws, st);
@@ -842,7 +895,7 @@ extern "C" int gpx_predict(const gpx_kernel_params *kp, int64_t S, int64_t n, in
     GPX_ARG_CHECK(ws != nullptr || gpx_predict_ws_bytes(S, n, kp->d) == 0, 15);
     if (S == 0 || M == 0) return 0;
     return predict_core(kp, S, n, M, x, xnew, W, ldw, alpha, m_new, m_const, diag_add, mu, var, M, M,
-                        true, ws, (cudaStream_t)stream);
+                        true, ws, (cudaStream_t)stream, predict_route_i8(kp, S, n, M));
 }
 
 // ---------------------------------------------------------------------------
@@ -898,11 +951,12 @@ extern "C" int gpx_predict_acq(const gpx_kernel_params *kp, int64_t S, int64_t n
     double *t_var = t_mu + (size_t)S * m_tile;
     const int d = kp->d;
     bool prep = true;
+    const bool i8 = predict_route_i8(kp, S, n, M);
     for (int64_t j0 = 0; j0 < M; j0 += m_tile) {
         const int64_t mt = (M - j0 < m_tile) ? (M - j0) : m_tile;
         int rc = predict_core(kp, S, n, mt, x, xnew + j0 * d, W, ldw, alpha,
                               m_new ? m_new + j0 : nullptr, m_const, diag_add, t_mu, t_var, mt, M,
-                              prep, ws, st);
+                              prep, ws, st, i8);
         if (rc) return rc;
         prep = false;
         const int64_t p0 = j0 / 32;   // gpx_acq_parts granularity

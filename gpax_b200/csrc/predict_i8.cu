@@ -152,6 +152,9 @@ __device__ __forceinline__ void bulk_load(uint32_t dst, const void *src, uint32_
                  "l"(src), "r"(bytes), "r"(bar)
                  : "memory");
 }
+__device__ __forceinline__ void bulk_prefetch_l2(const void *src, uint32_t bytes) {
+    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;\n" ::"l"(src), "r"(bytes) : "memory");
+}
 __device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;\n" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;\n" ::: "memory"); }
@@ -213,7 +216,7 @@ predict_i8_kernel(gpx_kernel_params kp, int n, int n128, int M, int S, const dou
                   const double *__restrict__ xnew, const int8_t *__restrict__ wsl, int64_t wsl_stride,
                   const int32_t *__restrict__ ew, unsigned char *__restrict__ scratch, int64_t scratch_stride,
                   const double *__restrict__ m_new, double m_const, const double *__restrict__ diag_add,
-                  double *__restrict__ mu, double *__restrict__ var, int64_t ldo, int64_t ldmn, int snake, int dbg) {
+                  double *__restrict__ mu, double *__restrict__ var, int64_t ldo, int64_t ldmn, int snake, int pf, int dbg) {
     // dbg (GPX_I8_DEBUG, profiling only): bit 0 skips the generator arithmetic, bit 1 the MMAs,
     // bit 2 the epilogue arithmetic, bit 3 the fixed-point conversion + byte stores, bit 4 the W loads
     using C = Cfg;
@@ -272,12 +275,23 @@ predict_i8_kernel(gpx_kernel_params kp, int n, int n128, int M, int S, const dou
 
         if (warp == GEN_WARPS + 1) {
             // ---- producer thread: per chunk one W slice block (stored in walk order) + the chunk's K* slices
-            if (lane == 0 && has_cur) {
+            if (lane == 0 && has_cur && !(dbg & 32)) {
                 const int8_t *src = wsl + (int64_t)s * wsl_stride;
                 int g = 0;
+                // L2 prefetch walker, PF chunks ahead of the loads: the smem ring (3 chunks ~ 2 us) covers an L2
+                // hit, not an HBM miss, and this CTA's K* store is only partly L2-resident (2 MB x 148 CTAs)
+                int gp = 0, rbp = 0, jp = 0;
+                auto prefetch_to = [&](int upto) {
+                    for (; gp < upto && rbp < T; ++gp) {
+                        if (!(dbg & 16)) bulk_prefetch_l2(src + (int64_t)gp * A_BLOCK, A_BLOCK);
+                        bulk_prefetch_l2(scr_cur + (size_t)walk_kc(rbp, jp, snake) * B_TILE, B_TILE);
+                        if (++jp == 4 * (rbp + 1)) { jp = 0; ++rbp; }
+                    }
+                };
                 for (int rb = 0; rb < T; ++rb) {
                     const int nk = 4 * (rb + 1);
                     for (int j = 0; j < nk; ++j, ++g) {
+                        if (pf > 0) prefetch_to(g + pf);
                         const int kc = walk_kc(rb, j, snake);
                         const int st = g % STAGES;
                         mbar_wait(b_empty + 8 * st, ((g / STAGES) & 1) ^ 1);   // MMAs of chunk g - STAGES retired
@@ -290,7 +304,7 @@ predict_i8_kernel(gpx_kernel_params kp, int n, int n128, int M, int S, const dou
             }
         } else if (warp == GEN_WARPS) {
             // ---- MMA issuer: 12 UTCIMMA per chunk, every descriptor one add away from a per-chunk base
-            if (lane == 0 && has_cur) {
+            if (lane == 0 && has_cur && !(dbg & 32)) {
                 const uint64_t descA0 = make_desc(s_stage, (MT / 8) * 128, 128);
                 const uint64_t descB0 = make_desc(s_stage + A_BLOCK, (B_ROWS / 8) * 128, 128);
                 const uint32_t iu1 = make_idesc(NT * 1, false), iu2 = make_idesc(NT * 2, false), iu3 = make_idesc(NT * 3, false),
@@ -370,7 +384,7 @@ predict_i8_kernel(gpx_kernel_params kp, int n, int n128, int M, int S, const dou
                     }
                 }
             };
-            int ep = has_cur ? 0 : T;                          // next row block whose planes this warp drains
+            int ep = (has_cur && !(dbg & 32)) ? 0 : T;                          // next row block whose planes this warp drains
             auto poll = [&]() {
                 while (ep < T) {
                     uint32_t ready = lane == 0 ? mbar_test(b_accFull, ep & 1) : 0u;
@@ -536,7 +550,8 @@ int i8_supported(const gpx_kernel_params *kp, int64_t n) {
 template <int KIND, int DMAX>
 int launch_i8(const gpx_kernel_params *kp, int64_t S, int64_t n, int64_t M, const double *x, const double *xnew,
               const double *W, int64_t ldw, const double *alpha, const double *m_new, double m_const,
-              const double *diag_add, double *mu, double *var, int prepare, char *ws, cudaStream_t st) {
+              const double *diag_add, double *mu, double *var, int64_t ldo, int64_t ldmn, int prepare, char *ws,
+              cudaStream_t st) {
     using namespace gpx;
     using namespace gpx::i8;
     const I8Layout L = i8_layout(S, n, DMAX);
@@ -545,6 +560,8 @@ int launch_i8(const gpx_kernel_params *kp, int64_t S, int64_t n, int64_t M, cons
     int8_t *wsl = (int8_t *)(ws + L.o_wsl);
     static int snake = -1;
     if (snake < 0) { const char *e = getenv("GPX_I8_SNAKE"); snake = e ? atoi(e) : 1; }
+    static int pf = -1;
+    if (pf < 0) { const char *e = getenv("GPX_I8_PF"); pf = e ? atoi(e) : 12; }
     if (prepare) {
         xs_prep_kernel<DMAX><<<dim3((unsigned)((L.n128 + 255) / 256), (unsigned)S), 256, 0, st>>>(*kp, (int)n, (int)L.n128, x, alpha, xs);
         w_rowexp_kernel<<<dim3((unsigned)(L.n128 / 8), (unsigned)S), 256, 0, st>>>((int)n, (int)L.n128, W, ldw, ew);
@@ -558,7 +575,7 @@ int launch_i8(const gpx_kernel_params *kp, int64_t S, int64_t n, int64_t M, cons
     const unsigned grid = (unsigned)(units < L.slots ? units : L.slots);
     predict_i8_kernel<KIND, DMAX><<<grid, THREADS, Cfg::BYTES, st>>>(
         *kp, (int)n, (int)L.n128, (int)M, (int)S, xs, xnew, wsl, L.wsl_stride, ew, (unsigned char *)(ws + L.o_scr), L.scr_stride,
-        m_new, m_const, diag_add, mu, var, M, M, snake, dbg);
+        m_new, m_const, diag_add, mu, var, ldo, ldmn, snake, pf, dbg);
     count_launches(1);
     return 0;
 }
@@ -568,6 +585,24 @@ extern "C" size_t gpx_predict_i8_ws_bytes(int64_t S, int64_t n, int32_t d) {
     if (S <= 0 || n <= 0) return 0;
     return i8_layout(S, n, d <= 2 ? 2 : 4).total;
 }
+
+namespace gpx {
+int predict_i8_supported(const gpx_kernel_params *kp, int64_t n) { return i8_supported(kp, n); }
+
+// strided core shared by gpx_predict_i8 and the attached-workspace route of gpx_predict / gpx_predict_acq
+int predict_i8_core(const gpx_kernel_params *kp, int64_t S, int64_t n, int64_t M, const double *x,
+                    const double *xnew, const double *W, int64_t ldw, const double *alpha,
+                    const double *m_new, double m_const, const double *diag_add, double *mu, double *var,
+                    int64_t ldo, int64_t ldmn, int prepare, void *ws, cudaStream_t st) {
+    int rc;
+    const bool d2 = kp->d <= 2;
+#define GPX_I8(KIND, DM) launch_i8<KIND, DM>(kp, S, n, M, x, xnew, W, ldw, alpha, m_new, m_const, diag_add, mu, var, ldo, ldmn, prepare, (char *)ws, st)
+    if (kp->kind == GPX_RBF) rc = d2 ? GPX_I8(GPX_RBF, 2) : GPX_I8(GPX_RBF, 4);
+    else rc = d2 ? GPX_I8(GPX_MATERN52, 2) : GPX_I8(GPX_MATERN52, 4);
+#undef GPX_I8
+    return rc;
+}
+}  // namespace gpx
 
 extern "C" int gpx_predict_i8(const gpx_kernel_params *kp, int64_t S, int64_t n, int64_t M,
                               const double *x, const double *xnew, const double *W, int64_t ldw,
@@ -589,14 +624,9 @@ extern "C" int gpx_predict_i8(const gpx_kernel_params *kp, int64_t S, int64_t n,
     GPX_ARG_CHECK(diag_add != nullptr, 12);
     GPX_ARG_CHECK(ws != nullptr, 16);
     if (S == 0 || M == 0) return 0;
-    cudaStream_t st = (cudaStream_t)stream;
-    int rc;
-    const bool d2 = kp->d <= 2;
-#define GPX_I8(KIND, DM) launch_i8<KIND, DM>(kp, S, n, M, x, xnew, W, ldw, alpha, m_new, m_const, diag_add, mu, var, prepare, (char *)ws, st)
-    if (kp->kind == GPX_RBF) rc = d2 ? GPX_I8(GPX_RBF, 2) : GPX_I8(GPX_RBF, 4);
-    else rc = d2 ? GPX_I8(GPX_MATERN52, 2) : GPX_I8(GPX_MATERN52, 4);
-#undef GPX_I8
-    if (rc) return rc;
+    if (int rc = predict_i8_core(kp, S, n, M, x, xnew, W, ldw, alpha, m_new, m_const, diag_add, mu, var, M, M,
+                                 prepare, ws, (cudaStream_t)stream))
+        return rc;
     GPX_LAUNCH_CHECK();
     return 0;
 }

@@ -6,8 +6,10 @@ anything here without a CUDA device raises.
 """
 from __future__ import annotations
 
+import contextlib
 import ctypes as C
 import math
+import threading
 
 import numpy as np
 import torch
@@ -176,6 +178,46 @@ def mll_grad(hpd: HyperParams, x, W, alpha, out=None, ws=None):
     return out
 
 
+_I8_SESSION = threading.local()
+
+
+@contextlib.contextmanager
+def i8_session(hpd, n, M, dev, same_factorisation=True):
+    """Attach an INT8-route workspace (``gpx_predict_i8_attach``) to this host thread for a block of
+    ``predict`` / ``predict_acq`` calls when ``gpx_predict_i8_want`` says the route would serve a call
+    with ``M`` candidates (RBF / Matern, d <= 4, 128 < n <= 4000, M >= 512, GPX_PREDICT_I8 != 0).
+    ``same_factorisation``: every call in the block uses the same W / x / alpha / hyper-parameters,
+    so W is sliced once.  The buffer goes back to torch's stream-ordered caching allocator at exit
+    (the kernels run on the current stream).  Yields whether the route is attached."""
+    want = 0 if getattr(_I8_SESSION, "active", False) else lib.gpx_predict_i8_want(C.byref(hpd.kp), hpd.S, n, M)
+    if not want:
+        yield getattr(_I8_SESSION, "active", False)
+        return
+    try:
+        buf = torch.empty(want // 8 + 1, dtype=F64, device=dev)
+    except torch.OutOfMemoryError:          # the FP64 route needs no extra memory
+        yield False
+        return
+    lib.gpx_predict_i8_attach(_ptr(buf), buf.numel() * 8, 1 if same_factorisation else 0)
+    _I8_SESSION.active = True
+    try:
+        yield True
+    finally:
+        _I8_SESSION.active = False
+        lib.gpx_predict_i8_attach(None, 0, 0)
+        del buf
+
+
+def _i8_route(hpd, n, M, dev):
+    """One-call session (no-op inside an ``i8_session``)."""
+    return i8_session(hpd, n, M, dev, same_factorisation=False)
+
+
+def predict_solver(hpd, n, M):
+    """Which kernel family ``predict`` / ``predict_acq`` use for this shape: ``"int8-ozaki"`` or ``"fp64-dmma"``."""
+    return "int8-ozaki" if lib.gpx_predict_i8_want(C.byref(hpd.kp), hpd.S, n, M) else "fp64-dmma"
+
+
 def predict_ws_alloc(S, n, d, dev):
     nbytes = lib.gpx_predict_ws_bytes(S, n, d)
     return torch.empty(max(1, nbytes // 8), dtype=F64, device=dev)
@@ -193,9 +235,10 @@ def predict(hpd: HyperParams, x, x_new, W, alpha, diag_add, m_new=None, m_const=
         mu = torch.empty((S, M), dtype=F64, device=dev)
     if want_var and var is None:
         var = torch.empty((S, M), dtype=F64, device=dev)
-    check(lib.gpx_predict(C.byref(hpd.kp), S, n, M, _ptr(x), _ptr(x_new), _ptr(W), W.shape[2],
-                          _ptr(alpha), _ptr(m_new), float(m_const), _ptr(diag_add), _ptr(mu),
-                          _ptr(var), _ptr(ws), _stream()), "gpx_predict")
+    with _i8_route(hpd, n, M, dev):
+        check(lib.gpx_predict(C.byref(hpd.kp), S, n, M, _ptr(x), _ptr(x_new), _ptr(W), W.shape[2],
+                              _ptr(alpha), _ptr(m_new), float(m_const), _ptr(diag_add), _ptr(mu),
+                              _ptr(var), _ptr(ws), _stream()), "gpx_predict")
     return mu, var
 
 
@@ -206,7 +249,8 @@ def predict_i8_ws_alloc(S, n, d, dev):
 def predict_i8(hpd: HyperParams, x, x_new, W, alpha, diag_add, m_new=None, m_const=1.0, mu=None, var=None,
                ws=None, prepare=True):
     """``gpx_predict_i8`` (EXPERIMENTAL): ``gpx_predict`` with the contraction emulated on the INT8
-    tensor cores (Ozaki splitting, 45 slice products); RBF / Matern, d <= 4, 128 < n <= 14000."""
+    tensor cores (Ozaki splitting: 8 byte slices per operand, 36 exact slice products); RBF / Matern,
+    d <= 4, 128 < n <= 4000.  ``predict`` / ``predict_acq`` route here by themselves (``_i8_route``)."""
     S, n, M = hpd.S, x.shape[0], x_new.shape[0]
     dev = x.device
     if ws is None:
@@ -260,12 +304,13 @@ def predict_acq(hpd: HyperParams, x, x_new, W, alpha, diag_add, acq, beta=10.0, 
     pi = torch.empty(P, dtype=torch.int64, device=dev)
     bv = torch.empty(1, dtype=F64, device=dev)
     bi = torch.empty(1, dtype=torch.int64, device=dev)
-    check(lib.gpx_predict_acq(C.byref(hpd.kp), S, n, M, _ptr(x), _ptr(x_new), _ptr(W), W.shape[2],
-                              _ptr(alpha), _ptr(m_new), float(m_const), _ptr(diag_add), int(acq),
-                              float(beta), float(y_max), float(mu_scale), float(mu_shift),
-                              float(sd_scale), int(m_offset), mt, _ptr(o_mu), _ptr(o_sd),
-                              _ptr(o_acq), _ptr(pv), _ptr(pi), _ptr(bv), _ptr(bi), _ptr(ws),
-                              _stream()), "gpx_predict_acq")
+    with _i8_route(hpd, n, M, dev):
+        check(lib.gpx_predict_acq(C.byref(hpd.kp), S, n, M, _ptr(x), _ptr(x_new), _ptr(W), W.shape[2],
+                                  _ptr(alpha), _ptr(m_new), float(m_const), _ptr(diag_add), int(acq),
+                                  float(beta), float(y_max), float(mu_scale), float(mu_shift),
+                                  float(sd_scale), int(m_offset), mt, _ptr(o_mu), _ptr(o_sd),
+                                  _ptr(o_acq), _ptr(pv), _ptr(pi), _ptr(bv), _ptr(bi), _ptr(ws),
+                                  _stream()), "gpx_predict_acq")
     return o_mu, o_sd, o_acq, bv, bi
 
 

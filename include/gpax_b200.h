@@ -42,7 +42,7 @@
 extern "C" {
 #endif
 
-#define GPX_ABI_VERSION 9
+#define GPX_ABI_VERSION 10
 
 /* covariance families: gpax/kernels.py:110 (RBF), :129 (Matern nu=5/2), :150 (Periodic) */
 enum { GPX_RBF = 0, GPX_MATERN52 = 1, GPX_PERIODIC = 2 };
@@ -166,20 +166,39 @@ int gpx_predict(const gpx_kernel_params *kp, int64_t S, int64_t n, int64_t M,
                 const double *m_new, double m_const, const double *diag_add,
                 double *mu, double *var, void *ws, void *stream);
 
-/* gpx_predict_i8 (EXPERIMENTAL): gpx_predict with the contraction V = W K*^T emulated on the INT8
- * tensor cores (tcgen05.mma kind::i8, INT32 accumulators in TMEM) by Ozaki splitting: the 8 bytes
- * of a 64-bit fixed-point value per operand, the 36 slice products of weight p + q < 8 (the count
- * BASELINE config 2 needs to match native FP64).  Same call site as gpx_predict (gpax/gp.py:277-301); only
- * RBF / Matern-5/2, d <= 4, 128 < n <= 4000 (else -3).  Arguments of gpx_predict plus
+/* gpx_predict_i8: gpx_predict with the contraction V = W K*^T emulated on the INT8 tensor cores
+ * (tcgen05.mma kind::i8, INT32 accumulators in TMEM) by Ozaki splitting: each fp64 operand becomes
+ * a 64-bit fixed-point integer (W: one exponent per row; K*: one per sample) whose 8 bytes are the
+ * int8 slices, and the 36 slice products of weight p + q < 8 are accumulated EXACTLY -- the count
+ * BASELINE config 2 needs to match native FP64; the result does not depend on the
+ * order of accumulation.  Same call site as gpx_predict (gpax/gp.py:277-301).  Only RBF /
+ * Matern-5/2, d <= 4, 128 < n <= 4000 (else -3).  Arguments of gpx_predict plus
  *   prepare != 0: (re)build the per-factorisation data in ws (row exponents and int8 slices of
  *                 W, staged training rows); pass 0 to sweep more candidates against the same W;
- *   ws: gpx_predict_i8_ws_bytes(S, n, d) bytes (~8.5 n^2 / 2 per sample). */
+ *   ws: gpx_predict_i8_ws_bytes(S, n, d) bytes: ~4.25 n^2 per sample for the W slices plus one
+ *       K* slice store (16 n bytes x 64 candidates x 2) per SM of the current device.
+ *
+ * Routing.  gpx_predict and gpx_predict_acq keep their signatures; a caller opts in per host
+ * thread by attaching a workspace:
+ *   gpx_predict_i8_want(kp, S, n, M): bytes to attach for the INT8 route to serve such a call, or
+ *       0 when it would not (unsupported shape, M < 512 -- the slicing of W is not amortised --
+ *       or GPX_PREDICT_I8=0 in the environment);
+ *   gpx_predict_i8_attach(ws, bytes, same_factorisation): from now on gpx_predict /
+ *       gpx_predict_acq called from THIS host thread route every call with 0 < want <= bytes
+ *       through the INT8 kernel (the `ws` argument of those calls is then unused but still
+ *       required); (NULL, 0, 0) detaches.  same_factorisation != 0 promises that every call until
+ *       the next attach uses the same W, x, alpha and hyper-parameters (a candidate sweep cut into
+ *       several calls): W is then sliced by the first routed call only.  Calls without an
+ *       attachment, gpx_predict_static and every unsupported shape run the FP64 DMMA kernels.
+ *       The buffer is the caller's; it must outlive the work queued on the stream. */
 size_t gpx_predict_i8_ws_bytes(int64_t S, int64_t n, int32_t d);
 int gpx_predict_i8(const gpx_kernel_params *kp, int64_t S, int64_t n, int64_t M,
                    const double *x, const double *xnew,
                    const double *W, int64_t ldw, const double *alpha,
                    const double *m_new, double m_const, const double *diag_add,
                    double *mu, double *var, int32_t prepare, void *ws, void *stream);
+size_t gpx_predict_i8_want(const gpx_kernel_params *kp, int64_t S, int64_t n, int64_t M);
+void gpx_predict_i8_attach(void *ws, size_t bytes, int32_t same_factorisation);
 
 /* gpx_predict_static: gpx_predict WITHOUT a caller workspace, for callers that cannot
  * allocate (code under CUDA graph capture, tight serving loops, harnesses that forbid
