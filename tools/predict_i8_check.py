@@ -11,7 +11,18 @@ wl = syn.config2(n=n, S=S, grid=grid)
 dev = torch.device("cuda:0")
 post = E.Posterior(wl.kind, wl.x, wl.y, wl.hp, device=dev)
 xn = E._dev(wl.x_new, dev)
-mu_r, var_r = E.predict(post.hpd, post.x, xn, post.W, post.alpha, post.hpd.jitter)
+import ctypes as C
+from gpax_b200 import _cabi
+pws = E.predict_ws_alloc(S, n, wl.d, dev)
+def dmma(mu=None, var=None):
+    """The FP64 DMMA route: gpx_predict with no INT8 workspace attached (engine.predict would attach one)."""
+    mu = torch.empty((S, wl.M), dtype=torch.float64, device=dev) if mu is None else mu
+    var = torch.empty_like(mu) if var is None else var
+    _cabi.check(_cabi.lib.gpx_predict(C.byref(post.hpd.kp), S, n, wl.M, E._ptr(post.x), E._ptr(xn), E._ptr(post.W),
+                                      post.W.shape[2], E._ptr(post.alpha), None, 1.0, E._ptr(post.hpd.jitter),
+                                      E._ptr(mu), E._ptr(var), E._ptr(pws), E._stream()), "gpx_predict")
+    return mu, var
+mu_r, var_r = dmma()
 torch.cuda.synchronize()
 ws = E.predict_i8_ws_alloc(S, n, wl.d, dev)
 mu_i, var_i = E.predict_i8(post.hpd, post.x, xn, post.W, post.alpha, post.hpd.jitter, ws=ws)
@@ -27,7 +38,7 @@ def t(fn, reps=2):
     e1.record(); torch.cuda.synchronize()
     return e0.elapsed_time(e1) / reps
 if S * wl.M * n * n > 1e11:
-    t64 = t(lambda: E.predict(post.hpd, post.x, xn, post.W, post.alpha, post.hpd.jitter, mu=mu_r, var=var_r))
+    t64 = t(lambda: dmma(mu_r, var_r))
     ti8 = t(lambda: E.predict_i8(post.hpd, post.x, xn, post.W, post.alpha, post.hpd.jitter, mu=mu_i, var=var_i, ws=ws))
     ti8n = t(lambda: E.predict_i8(post.hpd, post.x, xn, post.W, post.alpha, post.hpd.jitter, mu=mu_i, var=var_i, ws=ws, prepare=False))
     fl = S * wl.M * n * n
