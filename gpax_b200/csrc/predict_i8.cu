@@ -64,6 +64,11 @@ __host__ __device__ inline int64_t chunks_before(int rb) { return 2ll * rb * (rb
 __host__ __device__ __forceinline__ int walk_kc(int rb, int j, int snake) { return (snake && (rb & 1)) ? 4 * (rb + 1) - 1 - j : j; }
 
 // ---- once per factorisation: row exponents and int8 slices of W ---------------------------
+// Integers cannot carry a NaN: a row of W (failed factorisation) or a training point / hyper-parameter
+// that is not finite marks its row exponent, and the epilogue turns the mark back into NaN, so a
+// sample the FP64 route (and the reference) would answer with NaN is answered with NaN here too.
+constexpr int32_t EW_POISON = INT32_MIN / 2;
+
 // ew[s][row] = e with |W[row][k]| * 2^-e < 1 for all k <= row (0 for an all-zero / padding row)
 __global__ void __launch_bounds__(256)
 w_rowexp_kernel(int n, int n128, const double *__restrict__ W, int64_t ldw, int32_t *__restrict__ ew) {
@@ -71,13 +76,19 @@ w_rowexp_kernel(int n, int n128, const double *__restrict__ W, int64_t ldw, int3
     const int row = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
     if (row >= n128) return;
     double mx = 0.0;
+    bool bad = false;
     if (row < n) {
         const double *w = W + ((size_t)s * n + row) * ldw;
-        for (int k = lane; k <= row; k += 32) mx = fmax(mx, fabs(w[k]));
+        for (int k = lane; k <= row; k += 32) {
+            const double a = fabs(w[k]);
+            bad |= !(a <= 1.79769313486231570815e+308);          // NaN or Inf
+            mx = fmax(mx, a);
+        }
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, o));
-    if (lane == 0) ew[(size_t)s * n128 + row] = mx > 0.0 ? ilogb(mx) + 1 : 0;
+    bad = __any_sync(0xffffffffu, bad);
+    if (lane == 0) ew[(size_t)s * n128 + row] = bad ? EW_POISON : (mx > 0.0 ? ilogb(mx) + 1 : 0);
 }
 
 // one CTA = one (row block, chunk) of one sample: 128 x 32 values -> 8 canonical byte tiles
@@ -98,7 +109,8 @@ w_slice_kernel(int n, int n128, const double *__restrict__ W, int64_t ldw, const
         double v = 0.0;
         if (row < n && col <= row) v = W[((size_t)s * n + row) * ldw + col];
         // |v| < 2^e  ->  two's complement 64-bit fixed point; its bytes are the slices
-        const long long X = __double2ll_rd(scalbn(v, 63 - ew[(size_t)s * n128 + row]));
+        const int32_t er = ew[(size_t)s * n128 + row];
+        const long long X = er == EW_POISON ? 0ll : __double2ll_rd(scalbn(v, 63 - er));
         const int o = canon_off(r, k, MT);
 #pragma unroll
         for (int p = 0; p < NSL; ++p) blk[p * A_TILE + o] = (int8_t)(unsigned char)((unsigned long long)X >> (56 - 8 * p));
@@ -113,7 +125,7 @@ w_slice_kernel(int n, int n128, const double *__restrict__ W, int64_t ldw, const
 template <int DMAX>
 __global__ void __launch_bounds__(256)
 xs_prep_kernel(gpx_kernel_params kp, int n, int n128, const double *__restrict__ x,
-               const double *__restrict__ alpha, double *__restrict__ xs) {
+               const double *__restrict__ alpha, double *__restrict__ xs, int32_t *__restrict__ ew) {
     const int64_t s = blockIdx.y;
     const int k = blockIdx.x * 256 + threadIdx.x;
     if (k >= n128) return;
@@ -127,6 +139,8 @@ xs_prep_kernel(gpx_kernel_params kp, int n, int n128, const double *__restrict__
     }
     dst[DMAX * KC] = nrm;
     dst[(DMAX + 1) * KC] = k < n ? alpha[(size_t)s * n + k] : 0.0;
+    // runs after w_rowexp_kernel: a training point or hyper-parameter that is not finite poisons row k
+    if (k < n && !(fabs(nrm + kp.scale[s]) <= 1.79769313486231570815e+308)) ew[(size_t)s * n128 + k] = EW_POISON;
 }
 
 
@@ -367,7 +381,8 @@ predict_i8_kernel(gpx_kernel_params kp, int n, int n128, int M, int S, const dou
                 tc_fence_after();
                 const int row = rb * MT + quarter * 32 + lane;
                 // value = (X0 + X1 2^-24 + X2 2^-48) 2^(e_row + e_K - 15 - 16), X = three planes merged exactly in int64
-                const double sc = scalbn(1.0, ew[(size_t)s * n128 + row] + ekc - 31);
+                const int32_t erow = ew[(size_t)s * n128 + row];
+                const double sc = erow == EW_POISON ? __longlong_as_double(0x7ff8000000000000ll) : scalbn(1.0, erow + ekc - 31);
                 const uint32_t tl = tmem + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(half * 32);
 #pragma unroll
                 for (int jg = 0; jg < 4; ++jg) {
@@ -514,7 +529,10 @@ predict_i8_kernel(gpx_kernel_params kp, int n, int n128, int M, int S, const dou
             if (gj < M) {
                 const double kd = k_from_r2<KIND>(0.0, kp.scale[s]);
                 const double *pr = sRed + (t >> 5) * 4 * 32 + (t & 31);       // the four lane-quarter warps of this half
-                const double cs = (pr[0] + pr[32]) + (pr[64] + pr[96]);
+                double cs = (pr[0] + pr[32]) + (pr[64] + pr[96]);
+                double zs = 0.0;                                               // a candidate that is not finite answers NaN
+                for (int q = 0; q < kp.d; ++q) zs += xnew[(size_t)gj * kp.d + q] / len_of(kp, s, q);
+                if (!(fabs(zs) <= 1.79769313486231570815e+308)) cs = __longlong_as_double(0x7ff8000000000000ll);
                 if (var) var[(size_t)s * ldo + gj] = (kd + diag_add[s]) - cs;
                 if (mu) mu[(size_t)s * ldo + gj] = (m_new ? m_new[(size_t)s * ldmn + gj] : m_const) + sMeanCur[t];
             }
@@ -581,8 +599,8 @@ int launch_i8(const gpx_kernel_params *kp, int64_t S, int64_t n, int64_t M, cons
     static int pf = -1;
     if (pf < 0) { const char *e = getenv("GPX_I8_PF"); pf = e ? atoi(e) : 0; }
     if (prepare) {
-        xs_prep_kernel<DMAX><<<dim3((unsigned)((L.n128 + 255) / 256), (unsigned)S), 256, 0, st>>>(*kp, (int)n, (int)L.n128, x, alpha, xs);
         w_rowexp_kernel<<<dim3((unsigned)(L.n128 / 8), (unsigned)S), 256, 0, st>>>((int)n, (int)L.n128, W, ldw, ew);
+        xs_prep_kernel<DMAX><<<dim3((unsigned)((L.n128 + 255) / 256), (unsigned)S), 256, 0, st>>>(*kp, (int)n, (int)L.n128, x, alpha, xs, ew);
         w_slice_kernel<<<dim3((unsigned)L.nch, (unsigned)S), 256, 0, st>>>((int)n, (int)L.n128, W, ldw, ew, wsl, L.wsl_stride, snake);
         count_launches(3);
     }

@@ -242,3 +242,37 @@ def test_i8_route_is_cuda_graph_capturable(cuda):
     torch.cuda.synchronize()
     for a, e in zip(cap, eager):
         assert torch.equal(a, e)
+
+
+def test_i8_route_propagates_nan_like_the_fp64_route(cuda):
+    """Integers cannot hold a NaN: a sample whose factorisation failed (NaN rows in W), a hyper-parameter
+    or training point that is not finite, or a candidate that is not finite must still answer NaN -- the
+    same entries the FP64 route (and the reference's jnp arithmetic) answers NaN for, and nothing else."""
+    import torch
+    from gpax_b200 import engine as E
+    n, d, S, M = 300, 2, 4, 640
+    x, y, xn, hp = _mk("matern52", n, d, S, M, 17)
+    xn[7, 1] = np.nan                                         # one bad candidate
+    post = E.Posterior("matern52", x, y, hp, device=cuda)
+    post.W[1, 200, 10] = float("nan")                         # sample 1: a failed factorisation
+    post.alpha[1, :] = float("nan")
+    xn_d = E._dev(xn, cuda)
+    assert E.predict_solver(post.hpd, n, M) == "int8-ozaki"
+    mu, var = post.predict(xn)
+    mu_d, var_d = _dmma_predict(E, post, xn_d)
+    torch.cuda.synchronize()
+    assert torch.equal(torch.isnan(var), torch.isnan(var_d))
+    assert torch.equal(torch.isnan(mu), torch.isnan(mu_d))
+    assert bool(torch.isnan(var[1]).all()) and bool(torch.isnan(var[:, 7]).all())
+    ok = ~torch.isnan(var_d)
+    assert int(ok.sum()) == (S - 1) * (M - 1)
+    assert float(((var - var_d).abs()[ok]).max() / var_d[ok].abs().max()) < 1e-10
+    # a length scale that is not finite poisons the whole sample
+    hp2 = {k: v.copy() for k, v in hp.items()}
+    hp2["k_length"][2] = np.inf
+    post2 = E.Posterior("matern52", x, y, hp2, device=cuda)
+    xn[7, 1] = 0.0
+    mu2, var2 = post2.predict(xn)
+    mu2_d, var2_d = _dmma_predict(E, post2, E._dev(xn, cuda))
+    torch.cuda.synchronize()
+    assert torch.equal(torch.isnan(var2), torch.isnan(var2_d))
