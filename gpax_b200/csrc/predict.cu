@@ -814,7 +814,9 @@ extern "C" size_t gpx_predict_i8_want(const gpx_kernel_params *kp, int64_t S, in
     // (reads 8 n^2, writes 4 n^2 bytes per sample) is not amortised.
     static int enabled = -1;
     if (enabled < 0) { const char *e = getenv("GPX_PREDICT_I8"); enabled = (e && atoi(e) == 0) ? 0 : 1; }
-    if (!enabled || !kp || gpx::validate_kp(kp) != 0 || S <= 0 || M < 512) return 0;
+    static int64_t min_m = -1;              // GPX_PREDICT_I8_MIN_M: test hook, routes smaller sweeps too
+    if (min_m < 0) { const char *e = getenv("GPX_PREDICT_I8_MIN_M"); min_m = (e && atoll(e) > 0) ? atoll(e) : 512; }
+    if (!enabled || !kp || gpx::validate_kp(kp) != 0 || S <= 0 || M < min_m) return 0;
     if (!gpx::predict_i8_supported(kp, n)) return 0;
     return gpx_predict_i8_ws_bytes(S, n, kp->d);
 }

@@ -182,7 +182,7 @@ int gpx_predict(const gpx_kernel_params *kp, int64_t S, int64_t n, int64_t M,
  * thread by attaching a workspace:
  *   gpx_predict_i8_want(kp, S, n, M): bytes to attach for the INT8 route to serve such a call, or
  *       0 when it would not (unsupported shape, M < 512 -- the slicing of W is not amortised --
- *       or GPX_PREDICT_I8=0 in the environment);
+ *       or GPX_PREDICT_I8=0 in the environment; GPX_PREDICT_I8_MIN_M=<m> lowers the 512 for tests);
  *   gpx_predict_i8_attach(ws, bytes, same_factorisation): from now on gpx_predict /
  *       gpx_predict_acq called from THIS host thread route every call with 0 < want <= bytes
  *       through the INT8 kernel (the `ws` argument of those calls is then unused but still

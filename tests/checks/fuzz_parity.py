@@ -12,6 +12,7 @@ rng = np.random.default_rng(int(sys.argv[2]) if len(sys.argv) > 2 else 2024)
 dev = torch.device("cuda:0")
 rel = lambda a, b: float(np.max(np.abs(a - b)) / max(np.max(np.abs(b)), 1e-300))
 bad = 0
+routed = 0                    # cases the INT8 tensor-core route served (GPX_PREDICT_I8_MIN_M=1 routes every supported shape)
 worst = {"mu": 0.0, "var": 0.0}
 for c in range(cases):
     kind = ("rbf", "matern52", "periodic")[int(rng.integers(3))]
@@ -29,6 +30,7 @@ for c in range(cases):
     try:
         post = E.Posterior(kind, x, y, hp, m_train=mt, device=dev)
         mu, var = post.predict(xn, m_new=mn, observation_noise=obs)
+        routed += E.predict_solver(post.hpd, n, M) == "int8-ozaki"
         y_max, a, b, cc = float(y.max()), 1.2, -0.1, 1.2
         o_mu, o_sd, o_acq, pv, pi = E.acq_reduce(mu, var, _cabi.ACQ_EI, 0.0, y_max, a, b, cc, m_offset=7)
         bv, bi = E.argmax_finalize(pv, pi)
@@ -48,5 +50,6 @@ for c in range(cases):
     except Exception as ex:           # noqa: BLE001
         bad += 1
         print("ERROR", tag, repr(ex)[:200])
-print(f"fuzz_parity: {cases - bad}/{cases} cases ok; worst rel err mu {worst['mu']:.2e} var {worst['var']:.2e}")
+print(f"fuzz_parity: {cases - bad}/{cases} cases ok ({routed} through the INT8 route); worst rel err mu {worst['mu']:.2e} "
+      f"var {worst['var']:.2e}")
 sys.exit(1 if bad else 0)

@@ -35,7 +35,14 @@ def _both(cuda, post, xn, m_new):
     from gpax_b200._cabi import check, lib
     S, n, M = post.S, post.n, xn.shape[0]
     diag = post.hpd.jitter
-    mu_ref, var_ref = E.predict(post.hpd, post.x, xn, post.W, post.alpha, diag, m_new, 1.0)
+    # gpx_predict called directly with NO INT8 workspace attached: the FP64 kernels gpx_predict_static shares
+    # (engine.predict would route large sweeps through the INT8 kernel, equal to 1e-10 but not bit for bit)
+    mu_ref = torch.empty((S, M), dtype=torch.float64, device=cuda)
+    var_ref = torch.empty_like(mu_ref)
+    ws = E.predict_ws_alloc(S, n, post.hpd.d, cuda)
+    check(lib.gpx_predict(C.byref(post.hpd.kp), S, n, M, E._ptr(post.x), E._ptr(xn), E._ptr(post.W), post.W.shape[2],
+                          E._ptr(post.alpha), E._ptr(m_new), 1.0, E._ptr(diag), E._ptr(mu_ref), E._ptr(var_ref),
+                          E._ptr(ws), E._stream()), "gpx_predict")
     # outputs are allocated by the CALLER before the call; the entry point itself allocates nothing
     mu = torch.full((S, M), float("nan"), dtype=torch.float64, device=cuda)
     var = torch.full((S, M), float("nan"), dtype=torch.float64, device=cuda)
