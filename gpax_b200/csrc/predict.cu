@@ -830,7 +830,7 @@ extern "C" void gpx_predict_i8_attach(void *ws, size_t bytes, int32_t same_facto
 
 // the attached workspace serves this call (decided once per call, on the whole candidate count)
 static bool predict_route_i8(const gpx_kernel_params *kp, int64_t S, int64_t n, int64_t M) {
-    if (!tl_i8_ws) return false;
+    if (!tl_i8_ws || ((uintptr_t)tl_i8_ws & 255)) return false;      // bulk copies need the 256-byte aligned layout
     const size_t want = gpx_predict_i8_want(kp, S, n, M);
     return want > 0 && want <= tl_i8_bytes;
 }

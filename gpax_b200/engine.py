@@ -189,15 +189,21 @@ def i8_session(hpd, n, M, dev, same_factorisation=True):
     ``same_factorisation``: every call in the block uses the same W / x / alpha / hyper-parameters,
     so W is sliced once.  The buffer goes back to torch's stream-ordered caching allocator at exit
     (the kernels run on the current stream).  Yields whether the route is attached."""
-    want = 0 if getattr(_I8_SESSION, "active", False) else lib.gpx_predict_i8_want(C.byref(hpd.kp), hpd.S, n, M)
+    if getattr(_I8_SESSION, "active", False):       # nested: the outer session's attachment serves this call
+        yield True
+        return
+    want = lib.gpx_predict_i8_want(C.byref(hpd.kp), hpd.S, n, M)
     if not want:
-        yield getattr(_I8_SESSION, "active", False)
+        _I8_SESSION.last = "fp64-dmma"
+        yield False
         return
     try:
         buf = torch.empty(want // 8 + 1, dtype=F64, device=dev)
-    except torch.OutOfMemoryError:          # the FP64 route needs no extra memory
+    except torch.OutOfMemoryError:          # the FP64 route needs no extra memory; last_predict_route() says so
+        _I8_SESSION.last = "fp64-dmma (INT8 workspace of %d MiB did not fit)" % (want >> 20)
         yield False
         return
+    _I8_SESSION.last = "int8-ozaki"
     lib.gpx_predict_i8_attach(_ptr(buf), buf.numel() * 8, 1 if same_factorisation else 0)
     _I8_SESSION.active = True
     try:
@@ -211,6 +217,11 @@ def i8_session(hpd, n, M, dev, same_factorisation=True):
 def _i8_route(hpd, n, M, dev):
     """One-call session (no-op inside an ``i8_session``)."""
     return i8_session(hpd, n, M, dev, same_factorisation=False)
+
+
+def last_predict_route():
+    """The route the most recent ``predict`` / ``predict_acq`` / ``i8_session`` of this thread actually took."""
+    return getattr(_I8_SESSION, "last", None)
 
 
 def predict_solver(hpd, n, M):

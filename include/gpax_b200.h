@@ -190,7 +190,8 @@ int gpx_predict(const gpx_kernel_params *kp, int64_t S, int64_t n, int64_t M,
  *       the next attach uses the same W, x, alpha and hyper-parameters (a candidate sweep cut into
  *       several calls): W is then sliced by the first routed call only.  Calls without an
  *       attachment, gpx_predict_static and every unsupported shape run the FP64 DMMA kernels.
- *       The buffer is the caller's; it must outlive the work queued on the stream. */
+ *       The buffer is the caller's, 256-byte aligned (a misaligned one is ignored: FP64 route); it
+ *       must outlive the work queued on the stream. */
 size_t gpx_predict_i8_ws_bytes(int64_t S, int64_t n, int32_t d);
 int gpx_predict_i8(const gpx_kernel_params *kp, int64_t S, int64_t n, int64_t M,
                    const double *x, const double *xnew,
