@@ -161,6 +161,19 @@ __device__ __forceinline__ void sqrt_vec(double (&a)[N]) {
     }
 }
 
+// sin and cos of pi * x / p with the quotient carried in double-double and reduced mod 2
+// exactly, so the angle error is ~1e-16 absolute whatever |x / p| is (a plain
+// sincos(pi * x / p) loses |x/p| ulps, which the ill-conditioned solves then amplify)
+__device__ __forceinline__ void sincos_pi_ratio(double x, double p, double &sn, double &cs) {
+    const double hi = x / p;
+    const double lo = fma(-hi, p, x) / p;
+    const double r = hi - 2.0 * rint(0.5 * hi);
+    double s0, c0;
+    sincospi(r, &s0, &c0);
+    const double t = GPX_PI * lo;
+    sn = fma(c0, t, s0);
+    cs = fma(-s0, t, c0);
+}
 // N covariance values from N clipped scaled squared distances (in place),
 // same formulas / association order as k_from_r2
 template <int KIND, int N>

@@ -85,19 +85,6 @@ __host__ __device__ constexpr int dmax_of(int d) { return d <= 2 ? 2 : (d <= 4 ?
 // 3 FP64 instructions per dimension on the pipe the DMMAs need, instead of ~100.  The absolute
 // error of each sine stays at the 1e-16 level of the reference's own sin(pi * diff / period).
 constexpr int GPX_PERIODIC_FEAT = 3;
-// sin and cos of pi * x / p with the quotient carried in double-double and reduced mod 2
-// exactly, so the angle error is ~1e-16 absolute whatever |x / p| is (a plain
-// sincos(pi * x / p) loses |x/p| ulps, which the ill-conditioned solves then amplify)
-__device__ __forceinline__ void sincos_pi_ratio(double x, double p, double &sn, double &cs) {
-    const double hi = x / p;
-    const double lo = fma(-hi, p, x) / p;
-    const double r = hi - 2.0 * rint(0.5 * hi);
-    double s0, c0;
-    sincospi(r, &s0, &c0);
-    const double t = GPX_PI * lo;
-    sn = fma(c0, t, s0);
-    cs = fma(-s0, t, c0);
-}
 __host__ __device__ constexpr int feat_dim(int kind, int d) { return kind == GPX_PERIODIC_FEAT ? 2 * d : d; }
 
 // ---- mbarrier / TMA / shared-memory primitives (PTX) -------------------------

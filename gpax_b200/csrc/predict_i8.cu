@@ -1,7 +1,8 @@
 // gpx_predict_i8: the posterior-predictive contraction  V = W K*^T  (gpax/gp.py:297-299 through
 // W = L^-1, see predict.cu) emulated on the INT8 tensor cores (tcgen05.mma kind::i8, INT32
-// accumulators in TMEM) by Ozaki splitting, for n > 128, RBF / Matern-5/2, d <= 4.  EXPERIMENTAL,
-// selected only by GPX_PREDICT_I8=1 / this entry point; gpx_predict (FP64 DMMA) stays the default.
+// accumulators in TMEM) by Ozaki splitting, for 128 < n <= 4000: RBF / Matern-5/2 (d <= 8) and Periodic
+// (d <= 4, on its angle-addition features).  The default route of gpx_predict / gpx_predict_acq for callers
+// that attach a workspace (gpx_predict_i8_attach; engine.py does); GPX_PREDICT_I8=0 keeps the FP64 DMMA kernels.
 //
 // Numerics (tools/ozaki_feasibility.py).  Each fp64 operand becomes a 64-bit fixed-
 // point integer whose BYTES are the int8 slices (slicing costs nothing):
@@ -15,21 +16,27 @@
 // n = 2048); planes c < 8 are kept (36 slice products): measured error = native FP64's on BASELINE
 // config 2 including its cond(K) ~ 3e7 samples; 7 planes (28 products) miss 1e-10 by 50-100x.
 //
-// Mapping.  CTA = (sample, 64 candidates); it walks the 128-row blocks of W top to bottom and,
-// per block, the 32-wide k chunks left of / on the diagonal:
+// Mapping.  One persistent CTA per SM, 320 threads; unit = (sample, 64 candidates),
+// dealt round-robin so the CTAs in flight share a sample's W blocks in L2.  Per unit the CTA walks
+// the 128-row blocks of W top to bottom and, per block, the 32-wide k chunks left of / on the diagonal:
 //   A (W slices)  : 8 canonical K-major [128 x 32] byte tiles per chunk, pre-split once per
-//                   factorisation into one contiguous 32 KB block per (row block, chunk), bulk-
-//                   copied (cp.async.bulk + mbarrier) into a 5-stage ring together with the 32
-//                   staged training rows the generator needs;
-//   B (K* slices) : generated on chip in fp64 (reference operation order) by 8 warps (two per SM
-//                   sub-partition), converted to fixed point, its bytes transposed with PRMT and
-//                   stored STACKED along N ([8 x 64] x 32, double buffered): one W slice p meets
-//                   the K* slices q = 0..7-p in at most two MMAs (N <= 256) whose output columns are
-//                   the consecutive planes p..7 -- 12 MMAs per chunk instead of 36 (a small-N
-//                   UTCIMMA costs >= 34.5 ns whatever N is: tools/probe/tcgen05_i8_probe.cu);
+//                   factorisation into one contiguous 32 KB block per (row block, chunk) in walk order;
+//   B (K* slices) : generated ONCE per unit, one unit ahead of the MMAs, in fp64 (reference operation
+//                   order) by warps 0-7, converted to fixed point, bytes transposed with PRMT into the
+//                   canonical layout STACKED along N ([8 slices x 64 candidates] x 32 k, 16 KB per
+//                   chunk), assembled in shared memory and bulk-stored to this CTA's L2-resident
+//                   store (2 x n/32 chunks: this unit's and the next one's);
+//   loads         : warp 9, one thread: per chunk two cp.async.bulk (A block + K* chunk) into a
+//                   4-stage ring, mbarrier complete_tx; odd row blocks are walked right to left;
+//   MMAs          : warp 8, one thread: W slice p meets the stacked K* slices q = 0..7-p in at most
+//                   two tcgen05.mma kind::i8 (M 128, N <= 256, K 32) whose output columns are the
+//                   consecutive planes p..7 -- 12 per chunk instead of 36 (a small-N UTCIMMA costs
+//                   >= 34.5 ns whatever N is: tools/probe/tcgen05_i8_probe.cu); tcgen05.commit frees
+//                   the stage;
 //   D             : 8 planes x 64 columns = all 512 TMEM columns, lane = W row;
-//   epilogue      : per row block, tcgen05.ld -> fp64 Horner over the planes -> * 2^(e_row + e_K)
-//                   -> squared and accumulated per lane; the column sums are reduced once at the end.
+//   epilogue      : warps 0-7 again, per row block: tcgen05.ld, three planes merged exactly in int64,
+//                   biased int -> double, * 2^(e_row + e_K), squared and accumulated per lane; the
+//                   column sums are reduced once per unit.  Non-finite inputs answer NaN (EW_POISON).
 #include <cuda.h>
 #include <cstdlib>
 #include "common.cuh"
@@ -122,7 +129,10 @@ w_slice_kernel(int n, int n128, const double *__restrict__ W, int64_t ldw, const
 // covariances that meet zero W columns and alpha = 0).  A generator thread needs four consecutive k
 // of every component: 32 contiguous bytes, and the 8 k-groups of a warp tile a 256-byte line --
 // conflict-free, where row-major rows (128 bytes apart) were an 8-way bank conflict on every load.
-template <int DMAX>
+// Periodic (d <= 4) is staged as the angle-addition features of predict.cu (GPX_PERIODIC_FEAT): components
+// 2q, 2q + 1 = sin(pi x_q / p_q) / l_q, cos(pi x_q / p_q) / l_q; the candidate side holds (cos, -sin), so
+// one FMA pair gives sin(pi (x - x') / p) / l and the kernel is scale * exp(-2 sum of its squares).
+template <int KIND, int DMAX>
 __global__ void __launch_bounds__(256)
 xs_prep_kernel(gpx_kernel_params kp, int n, int n128, const double *__restrict__ x,
                const double *__restrict__ alpha, double *__restrict__ xs, int32_t *__restrict__ ew) {
@@ -131,13 +141,30 @@ xs_prep_kernel(gpx_kernel_params kp, int n, int n128, const double *__restrict__
     if (k >= n128) return;
     double *dst = xs + ((size_t)s * n128 + (size_t)(k / KC) * KC) * (DMAX + 2) + (k % KC);
     double nrm = 0.0;
+    if (KIND == GPX_PERIODIC) {
 #pragma unroll
-    for (int q = 0; q < DMAX; ++q) {
-        double v = (k < n && q < kp.d) ? x[(size_t)k * kp.d + q] / len_of(kp, s, q) : 0.0;
-        dst[q * KC] = v;
-        nrm += v * v;
+        for (int q = 0; q < DMAX / 2; ++q) {
+            double sn = 0.0, cs = 0.0;
+            if (k < n && q < kp.d) {
+                sincos_pi_ratio(x[(size_t)k * kp.d + q], per_of(kp, s, q), sn, cs);
+                const double l = len_of(kp, s, q);
+                sn /= l;
+                cs /= l;
+            }
+            dst[(2 * q) * KC] = sn;
+            dst[(2 * q + 1) * KC] = cs;
+            nrm += sn + cs;                                   // only its finiteness is used below
+        }
+        dst[DMAX * KC] = 0.0;
+    } else {
+#pragma unroll
+        for (int q = 0; q < DMAX; ++q) {
+            double v = (k < n && q < kp.d) ? x[(size_t)k * kp.d + q] / len_of(kp, s, q) : 0.0;
+            dst[q * KC] = v;
+            nrm += v * v;
+        }
+        dst[DMAX * KC] = nrm;
     }
-    dst[DMAX * KC] = nrm;
     dst[(DMAX + 1) * KC] = k < n ? alpha[(size_t)s * n + k] : 0.0;
     // runs after w_rowexp_kernel: a training point or hyper-parameter that is not finite poisons row k
     if (k < n && !(fabs(nrm + kp.scale[s]) <= 1.79769313486231570815e+308)) ew[(size_t)s * n128 + k] = EW_POISON;
@@ -429,11 +456,21 @@ predict_i8_kernel(gpx_kernel_params kp, int n, int n128, int M, int S, const dou
                 for (int i = 0; i < 2; ++i) {
                     const int gj = jn + cb + 32 * i;
                     double nrm = 0.0;
+                    if (KIND == GPX_PERIODIC) {
 #pragma unroll
-                    for (int q = 0; q < DMAX; ++q) {
-                        const double v = (gj < M && q < kp.d) ? xnew[(size_t)gj * kp.d + q] / len_of(kp, sn, q) : 0.0;
-                        z[i][q] = v;
-                        nrm += v * v;
+                        for (int q = 0; q < DMAX / 2; ++q) {
+                            double sv = 0.0, cv = 0.0;
+                            if (gj < M && q < kp.d) sincos_pi_ratio(xnew[(size_t)gj * kp.d + q], per_of(kp, sn, q), sv, cv);
+                            z[i][2 * q] = cv;
+                            z[i][2 * q + 1] = -sv;
+                        }
+                    } else {
+#pragma unroll
+                        for (int q = 0; q < DMAX; ++q) {
+                            const double v = (gj < M && q < kp.d) ? xnew[(size_t)gj * kp.d + q] / len_of(kp, sn, q) : 0.0;
+                            z[i][q] = v;
+                            nrm += v * v;
+                        }
                     }
                     z[i][DMAX] = nrm;
                 }
@@ -441,30 +478,63 @@ predict_i8_kernel(gpx_kernel_params kp, int n, int n128, int M, int S, const dou
                 double macc[2] = {0.0, 0.0};
                 const double *xs_s = xs + (size_t)sn * n128 * XSP;
                 for (int kc = 0; kc < NKC; ++kc) {
-                    double xr[4][XSP];
-                    const double2 *colp = reinterpret_cast<const double2 *>(xs_s + (size_t)kc * KC * XSP + 4 * kq);
+                    // squared scaled distance (RBF / Matern) or 4 * sum sin^2(pi dx / p) / l^2 (Periodic: the RBF
+                    // formula exp(-v / 2) then gives exp(-2 sum ...), scaling by 4 is exact) of 4 k x 2 candidates
+                    auto dist = [&](const double *zi, const double *row) {
+                        if (KIND == GPX_PERIODIC) {
+                            double acc = 0.0;
 #pragma unroll
-                    for (int q = 0; q < XSP; ++q) {
-                        const double2 lo2 = __ldg(colp + q * (KC / 2)), hi2 = __ldg(colp + q * (KC / 2) + 1);
-                        xr[0][q] = lo2.x;
-                        xr[1][q] = lo2.y;
-                        xr[2][q] = hi2.x;
-                        xr[3][q] = hi2.y;
-                    }
-                    double v[2][4];
-#pragma unroll
-                    for (int i = 0; i < 2; ++i) {
-#pragma unroll
-                        for (int r = 0; r < 4; ++r) {
+                            for (int q = 0; q < DMAX; q += 2) {
+                                const double sd = fma(zi[q], row[q], zi[q + 1] * row[q + 1]);
+                                acc = fma(sd, sd, acc);
+                            }
+                            return 4.0 * acc;
+                        } else {
                             double xz = 0.0;
 #pragma unroll
-                            for (int q = 0; q < DMAX; ++q) xz = fma(z[i][q], xr[r][q], xz);
-                            const double r2 = (z[i][DMAX] - 2.0 * xz) + xr[r][DMAX];
-                            v[i][r] = r2 < 0.0 ? 0.0 : r2;
+                            for (int q = 0; q < DMAX; ++q) xz = fma(zi[q], row[q], xz);
+                            const double r2 = (zi[DMAX] - 2.0 * xz) + row[DMAX];
+                            return r2 < 0.0 ? 0.0 : r2;
                         }
-                        if (!(dbg & 1)) k_from_r2_vec<KIND, 4>(v[i], scale);
+                    };
+                    constexpr int KG = (KIND == GPX_PERIODIC) ? GPX_RBF : KIND;
+                    double v[2][4], al[4];
+                    const double *chunk = xs_s + (size_t)kc * KC * XSP + 4 * kq;
+                    if (DMAX <= 4) {
+                        double xr[4][XSP];
+                        const double2 *colp = reinterpret_cast<const double2 *>(chunk);
 #pragma unroll
-                        for (int r = 0; r < 4; ++r) macc[i] = fma(v[i][r], xr[r][DMAX + 1], macc[i]);
+                        for (int q = 0; q < XSP; ++q) {
+                            const double2 lo2 = __ldg(colp + q * (KC / 2)), hi2 = __ldg(colp + q * (KC / 2) + 1);
+                            xr[0][q] = lo2.x;
+                            xr[1][q] = lo2.y;
+                            xr[2][q] = hi2.x;
+                            xr[3][q] = hi2.y;
+                        }
+#pragma unroll
+                        for (int r = 0; r < 4; ++r) {
+                            v[0][r] = dist(z[0], xr[r]);
+                            v[1][r] = dist(z[1], xr[r]);
+                            al[r] = xr[r][DMAX + 1];
+                        }
+                    } else {
+                        // wide rows (5 .. 8 features): one training point at a time, or 4 x 10 doubles of rows
+                        // would not fit beside the 64 registers of column sums
+#pragma unroll
+                        for (int r = 0; r < 4; ++r) {
+                            double row[XSP];
+#pragma unroll
+                            for (int q = 0; q < XSP; ++q) row[q] = __ldg(chunk + q * KC + r);
+                            v[0][r] = dist(z[0], row);
+                            v[1][r] = dist(z[1], row);
+                            al[r] = row[DMAX + 1];
+                        }
+                    }
+#pragma unroll
+                    for (int i = 0; i < 2; ++i) {
+                        if (!(dbg & 1)) k_from_r2_vec<KG, 4>(v[i], scale);
+#pragma unroll
+                        for (int r = 0; r < 4; ++r) macc[i] = fma(v[i][r], al[r], macc[i]);
                     }
                     // the chunk is assembled in shared memory and leaves as ONE 16 KB bulk store (async proxy end
                     // to end): 4-byte generic-proxy stores to global made the sweep 2 ms (4 %) slower
@@ -527,11 +597,12 @@ predict_i8_kernel(gpx_kernel_params kp, int n, int n128, int M, int S, const dou
         if (t < NT && has_cur) {
             const int gj = j0 + t;
             if (gj < M) {
-                const double kd = k_from_r2<KIND>(0.0, kp.scale[s]);
+                const double kd = k_from_r2<(KIND == GPX_PERIODIC) ? GPX_RBF : KIND>(0.0, kp.scale[s]);
                 const double *pr = sRed + (t >> 5) * 4 * 32 + (t & 31);       // the four lane-quarter warps of this half
                 double cs = (pr[0] + pr[32]) + (pr[64] + pr[96]);
                 double zs = 0.0;                                               // a candidate that is not finite answers NaN
-                for (int q = 0; q < kp.d; ++q) zs += xnew[(size_t)gj * kp.d + q] / len_of(kp, s, q);
+                for (int q = 0; q < kp.d; ++q)
+                    zs += xnew[(size_t)gj * kp.d + q] / len_of(kp, s, q) + (KIND == GPX_PERIODIC ? 1.0 / per_of(kp, s, q) : 0.0);
                 if (!(fabs(zs) <= 1.79769313486231570815e+308)) cs = __longlong_as_double(0x7ff8000000000000ll);
                 if (var) var[(size_t)s * ldo + gj] = (kd + diag_add[s]) - cs;
                 if (mu) mu[(size_t)s * ldo + gj] = (m_new ? m_new[(size_t)s * ldmn + gj] : m_const) + sMeanCur[t];
@@ -579,8 +650,20 @@ I8Layout i8_layout(int64_t S, int64_t n, int dmax) {
     L.total = o;
     return L;
 }
+// staged feature width: Periodic runs on 2 d angle-addition features (d <= 4, as in predict.cu; not when
+// GPX_PERIODIC_SINE=1 asks for the per-pair sine), RBF / Matern on their d coordinates
+int i8_feat_dim(const gpx_kernel_params *kp) {
+    if (kp->kind == GPX_PERIODIC) {
+        static int force_sine = -1;
+        if (force_sine < 0) { const char *e = getenv("GPX_PERIODIC_SINE"); force_sine = (e && atoi(e)) ? 1 : 0; }
+        return (kp->d <= GPX_MAX_D / 2 && !force_sine) ? 2 * kp->d : 99;
+    }
+    return kp->d;
+}
+int i8_dmax(int fd) { return fd <= 2 ? 2 : (fd <= 4 ? 4 : 8); }
 int i8_supported(const gpx_kernel_params *kp, int64_t n) {
-    return (kp->kind == GPX_RBF || kp->kind == GPX_MATERN52) && kp->d <= 4 && n > 128 && n <= 4000;
+    return (kp->kind == GPX_RBF || kp->kind == GPX_MATERN52 || kp->kind == GPX_PERIODIC) && i8_feat_dim(kp) <= 8 &&
+           n > 128 && n <= 4000;
 }
 
 template <int KIND, int DMAX>
@@ -600,7 +683,7 @@ int launch_i8(const gpx_kernel_params *kp, int64_t S, int64_t n, int64_t M, cons
     if (pf < 0) { const char *e = getenv("GPX_I8_PF"); pf = e ? atoi(e) : 0; }
     if (prepare) {
         w_rowexp_kernel<<<dim3((unsigned)(L.n128 / 8), (unsigned)S), 256, 0, st>>>((int)n, (int)L.n128, W, ldw, ew);
-        xs_prep_kernel<DMAX><<<dim3((unsigned)((L.n128 + 255) / 256), (unsigned)S), 256, 0, st>>>(*kp, (int)n, (int)L.n128, x, alpha, xs, ew);
+        xs_prep_kernel<KIND, DMAX><<<dim3((unsigned)((L.n128 + 255) / 256), (unsigned)S), 256, 0, st>>>(*kp, (int)n, (int)L.n128, x, alpha, xs, ew);
         w_slice_kernel<<<dim3((unsigned)L.nch, (unsigned)S), 256, 0, st>>>((int)n, (int)L.n128, W, ldw, ew, wsl, L.wsl_stride, snake);
         count_launches(3);
     }
@@ -619,7 +702,7 @@ int launch_i8(const gpx_kernel_params *kp, int64_t S, int64_t n, int64_t M, cons
 
 extern "C" size_t gpx_predict_i8_ws_bytes(int64_t S, int64_t n, int32_t d) {
     if (S <= 0 || n <= 0) return 0;
-    return i8_layout(S, n, d <= 2 ? 2 : 4).total;
+    return i8_layout(S, n, i8_dmax(d <= GPX_MAX_D / 2 ? 2 * d : d)).total;      // widest staging of any kind (Periodic: 2 d)
 }
 
 namespace gpx {
@@ -631,10 +714,13 @@ int predict_i8_core(const gpx_kernel_params *kp, int64_t S, int64_t n, int64_t M
                     const double *m_new, double m_const, const double *diag_add, double *mu, double *var,
                     int64_t ldo, int64_t ldmn, int prepare, void *ws, cudaStream_t st) {
     int rc;
-    const bool d2 = kp->d <= 2;
+    const int dm = i8_dmax(i8_feat_dim(kp));
 #define GPX_I8(KIND, DM) launch_i8<KIND, DM>(kp, S, n, M, x, xnew, W, ldw, alpha, m_new, m_const, diag_add, mu, var, ldo, ldmn, prepare, (char *)ws, st)
-    if (kp->kind == GPX_RBF) rc = d2 ? GPX_I8(GPX_RBF, 2) : GPX_I8(GPX_RBF, 4);
-    else rc = d2 ? GPX_I8(GPX_MATERN52, 2) : GPX_I8(GPX_MATERN52, 4);
+#define GPX_I8_D(KIND) (dm == 2 ? GPX_I8(KIND, 2) : (dm == 4 ? GPX_I8(KIND, 4) : GPX_I8(KIND, 8)))
+    if (kp->kind == GPX_RBF) rc = GPX_I8_D(GPX_RBF);
+    else if (kp->kind == GPX_MATERN52) rc = GPX_I8_D(GPX_MATERN52);
+    else rc = GPX_I8_D(GPX_PERIODIC);
+#undef GPX_I8_D
 #undef GPX_I8
     return rc;
 }
@@ -649,8 +735,8 @@ extern "C" int gpx_predict_i8(const gpx_kernel_params *kp, int64_t S, int64_t n,
     GPX_ARG_CHECK(validate_kp(kp) == 0, 1);
     GPX_ARG_CHECK(S >= 0 && S <= 65535, 2);
     if (!i8_supported(kp, n)) {
-        set_error("gpx_predict_i8: only RBF / Matern-5/2 with d <= 4 and 128 < n <= 4000 (got kind %d, d %d, n %lld); "
-                  "use gpx_predict", kp->kind, kp->d, (long long)n);
+        set_error("gpx_predict_i8: only RBF / Matern-5/2 (d <= 8) / Periodic (d <= 4) with 128 < n <= 4000 (got kind %d, "
+                  "d %d, n %lld); use gpx_predict", kp->kind, kp->d, (long long)n);
         return -3;
     }
     GPX_ARG_CHECK(M >= 0 && M < (1ll << 31) - 512, 4);

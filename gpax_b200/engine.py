@@ -185,7 +185,7 @@ _I8_SESSION = threading.local()
 def i8_session(hpd, n, M, dev, same_factorisation=True):
     """Attach an INT8-route workspace (``gpx_predict_i8_attach``) to this host thread for a block of
     ``predict`` / ``predict_acq`` calls when ``gpx_predict_i8_want`` says the route would serve a call
-    with ``M`` candidates (RBF / Matern, d <= 4, 128 < n <= 4000, M >= 512, GPX_PREDICT_I8 != 0).
+    with ``M`` candidates (RBF / Matern d <= 8, Periodic d <= 4; 128 < n <= 4000, M >= 512, GPX_PREDICT_I8 != 0).
     ``same_factorisation``: every call in the block uses the same W / x / alpha / hyper-parameters,
     so W is sliced once.  The buffer goes back to torch's stream-ordered caching allocator at exit
     (the kernels run on the current stream).  Yields whether the route is attached."""
@@ -260,8 +260,8 @@ def predict_i8_ws_alloc(S, n, d, dev):
 def predict_i8(hpd: HyperParams, x, x_new, W, alpha, diag_add, m_new=None, m_const=1.0, mu=None, var=None,
                ws=None, prepare=True):
     """``gpx_predict_i8`` (EXPERIMENTAL): ``gpx_predict`` with the contraction emulated on the INT8
-    tensor cores (Ozaki splitting: 8 byte slices per operand, 36 exact slice products); RBF / Matern,
-    d <= 4, 128 < n <= 4000.  ``predict`` / ``predict_acq`` route here by themselves (``_i8_route``)."""
+    tensor cores (Ozaki splitting: 8 byte slices per operand, 36 exact slice products); RBF / Matern
+    (d <= 8), Periodic (d <= 4), 128 < n <= 4000.  ``predict`` / ``predict_acq`` route here by themselves (``_i8_route``)."""
     S, n, M = hpd.S, x.shape[0], x_new.shape[0]
     dev = x.device
     if ws is None:

@@ -171,8 +171,9 @@ int gpx_predict(const gpx_kernel_params *kp, int64_t S, int64_t n, int64_t M,
  * a 64-bit fixed-point integer (W: one exponent per row; K*: one per sample) whose 8 bytes are the
  * int8 slices, and the 36 slice products of weight p + q < 8 are accumulated EXACTLY -- the count
  * BASELINE config 2 needs to match native FP64; the result does not depend on the
- * order of accumulation.  Same call site as gpx_predict (gpax/gp.py:277-301).  Only RBF /
- * Matern-5/2, d <= 4, 128 < n <= 4000 (else -3).  Arguments of gpx_predict plus
+ * order of accumulation.  Same call site as gpx_predict (gpax/gp.py:277-301).  RBF / Matern-5/2
+ * (d <= 8) and Periodic (d <= 4, through its 2 d angle-addition features), 128 < n <= 4000 (else
+ * -3).  Arguments of gpx_predict plus
  *   prepare != 0: (re)build the per-factorisation data in ws (row exponents and int8 slices of
  *                 W, staged training rows); pass 0 to sweep more candidates against the same W;
  *   ws: gpx_predict_i8_ws_bytes(S, n, d) bytes: ~4.25 n^2 per sample for the W slices plus one

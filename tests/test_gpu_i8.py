@@ -46,8 +46,9 @@ def test_route_selection(cuda):
         assert solver("rbf", 300, 2, 3, 511) == "fp64-dmma"      # slicing not amortised
     assert solver("rbf", 128, 2, 3, 600) == "fp64-dmma"          # one-slab kernels below
     assert solver("rbf", 4001, 2, 1, 600) == "fp64-dmma"         # INT32 planes would overflow
-    assert solver("rbf", 300, 5, 3, 600) == "fp64-dmma"
-    assert solver("periodic", 300, 2, 3, 600, per=True) == "fp64-dmma"
+    assert solver("rbf", 300, 8, 3, 600) == "int8-ozaki"          # wide rows: one training point at a time
+    assert solver("periodic", 300, 3, 3, 600, per=True) == "int8-ozaki"      # 2 d = 6 angle-addition features
+    assert solver("periodic", 300, 5, 3, 600, per=True) == "fp64-dmma"       # 2 d > 8: per-pair sine kernels
 
 
 def test_route_env_switch():
@@ -83,6 +84,31 @@ def test_i8_route_matches_oracle(cuda, kind, n, d, S, M):
     # variance is k** - |v|^2 with up to five digits cancelled: 2e-11 of max var measured at n = 2048)
     mu_d, var_d = _dmma_predict(E, post, E._dev(xn, cuda))
     torch.cuda.synchronize()
+    assert _rel(mu.cpu().numpy(), mu_d.cpu().numpy()) < 1e-10
+    assert _rel(var.cpu().numpy(), var_d.cpu().numpy()) < 1e-10
+
+
+@pytest.mark.parametrize("kind,n,d,S,M,ard", [("periodic", 300, 1, 3, 600, False), ("periodic", 700, 2, 2, 640, True),
+                                              ("periodic", 1024, 3, 2, 1000, False), ("periodic", 260, 4, 2, 512, True),
+                                              ("rbf", 400, 6, 2, 600, True), ("matern52", 520, 8, 2, 700, False),
+                                              ("matern52", 300, 5, 3, 513, True)])
+def test_i8_route_periodic_and_wide_rows(cuda, kind, n, d, S, M, ard):
+    """Periodic through its angle-addition features (2 d <= 8 staged components) and RBF / Matern with
+    5 .. 8 input dimensions (rows read one training point at a time): oracle parity at the bar of
+    the FP64 route for the same shapes (Periodic: 3e-10, the documented feature-form bound of DESIGN.md 2;
+    the others 1e-10), and agreement with the FP64 route."""
+    import torch
+    from gpax_b200 import engine as E
+    x, y, xn, hp = _mk(kind, n, d, S, M, 1300 + n + d, ard=ard, period=(kind == "periodic"))
+    post = E.Posterior(kind, x, y, hp, device=cuda)
+    assert E.predict_solver(post.hpd, n, M) == "int8-ozaki"
+    mu, var = post.predict(xn)
+    mu_d, var_d = _dmma_predict(E, post, E._dev(xn, cuda))
+    torch.cuda.synchronize()
+    mu_r, var_r = O.predict_batched(kind, x, y, xn, hp, use_cholesky=True)
+    tol = 3e-10 if kind == "periodic" else 1e-10
+    assert _rel(mu.cpu().numpy(), mu_r) < tol
+    assert _rel(var.cpu().numpy(), var_r) < tol
     assert _rel(mu.cpu().numpy(), mu_d.cpu().numpy()) < 1e-10
     assert _rel(var.cpu().numpy(), var_d.cpu().numpy()) < 1e-10
 
@@ -208,7 +234,7 @@ def test_i8_direct_entry_point_errors(cuda):
     import ctypes as C
     import torch
     from gpax_b200 import engine as E, _cabi
-    x, y, xn, hp = _mk("periodic", 200, 2, 2, 600, 3, period=True)
+    x, y, xn, hp = _mk("periodic", 200, 5, 2, 600, 3, period=True)
     post = E.Posterior("periodic", x, y, hp, device=cuda)
     with pytest.raises(_cabi.GpxError, match="only RBF / Matern-5/2"):
         E.predict_i8(post.hpd, post.x, E._dev(xn, cuda), post.W, post.alpha, post.hpd.jitter)
