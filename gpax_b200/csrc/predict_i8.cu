@@ -110,6 +110,8 @@ w_slice_kernel(int n, int n128, const double *__restrict__ W, int64_t ldw, const
     while (chunks_before(rb + 1) <= id) ++rb;
     const int kc = walk_kc(rb, id - (int)chunks_before(rb), snake);
     int8_t *blk = out + s * sample_stride + (int64_t)id * A_BLOCK;
+    // phase 1: coalesced read (a warp = one 256-byte row segment), fixed point into shared memory
+    __shared__ long long sX[MT][KC + 1];
     for (int e = threadIdx.x; e < MT * KC; e += 256) {
         const int r = e >> 5, k = e & 31;
         const int row = rb * MT + r, col = kc * KC + k;
@@ -117,10 +119,24 @@ w_slice_kernel(int n, int n128, const double *__restrict__ W, int64_t ldw, const
         if (row < n && col <= row) v = W[((size_t)s * n + row) * ldw + col];
         // |v| < 2^e  ->  two's complement 64-bit fixed point; its bytes are the slices
         const int32_t er = ew[(size_t)s * n128 + row];
-        const long long X = er == EW_POISON ? 0ll : __double2ll_rd(scalbn(v, 63 - er));
-        const int o = canon_off(r, k, MT);
+        sX[r][k] = er == EW_POISON ? 0ll : __double2ll_rd(scalbn(v, 63 - er));
+    }
+    __syncthreads();
+    // phase 2: thread = (row, k half): the 16 bytes of one canonical core-matrix row per slice, one
+    // 16-byte store each (byte stores made this kernel 13.4 ms per C2 step)
+    const int r = threadIdx.x >> 1, h = threadIdx.x & 1;
+    unsigned long long x[16];
 #pragma unroll
-        for (int p = 0; p < NSL; ++p) blk[p * A_TILE + o] = (int8_t)(unsigned char)((unsigned long long)X >> (56 - 8 * p));
+    for (int i = 0; i < 16; ++i) x[i] = (unsigned long long)sX[r][16 * h + i];
+    const int o = canon_off(r, 16 * h, MT);
+#pragma unroll
+    for (int p = 0; p < NSL; ++p) {
+        uint32_t w[4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q)
+            w[q] = (uint32_t)((x[4 * q] >> (56 - 8 * p)) & 0xff) | ((uint32_t)((x[4 * q + 1] >> (56 - 8 * p)) & 0xff) << 8) |
+                   ((uint32_t)((x[4 * q + 2] >> (56 - 8 * p)) & 0xff) << 16) | ((uint32_t)((x[4 * q + 3] >> (56 - 8 * p)) & 0xff) << 24);
+        *reinterpret_cast<uint4 *>(blk + p * A_TILE + o) = make_uint4(w[0], w[1], w[2], w[3]);
     }
 }
 
