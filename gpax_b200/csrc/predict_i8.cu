@@ -38,6 +38,7 @@
 //                   biased int -> double, * 2^(e_row + e_K), squared and accumulated per lane; the
 //                   column sums are reduced once per unit.  Non-finite inputs answer NaN (EW_POISON).
 #include <cuda.h>
+#include <cstdio>
 #include <cstdlib>
 #include "common.cuh"
 
@@ -285,7 +286,8 @@ predict_i8_kernel(gpx_kernel_params kp, int n, int n128, int M, int S, const dou
                   double *__restrict__ mu, double *__restrict__ var, int64_t ldo, int64_t ldmn, int snake, int pf, int dbg) {
     // dbg (GPX_I8_DEBUG, profiling only): bit 0 skips the generator arithmetic, bit 1 the MMAs,
     // bit 2 the epilogue arithmetic, bit 3 the fixed-point conversion + byte stores, bit 4 the W loads,
-    // bit 5 everything but the generator, bit 6 the bulk store of the K* chunk
+    // bit 5 everything but the generator, bit 6 the bulk store of the K* chunk, bit 8 prints where the
+    // MMA-issuing thread's cycles go
     using C = Cfg;
     constexpr int XSP = DMAX + 2;
     extern __shared__ unsigned char smem_raw[];
@@ -317,6 +319,9 @@ predict_i8_kernel(gpx_kernel_params kp, int n, int n128, int M, int S, const dou
     // Iteration i works on unit `cur` (bulk loads, MMAs, epilogues) while the generator warps produce the
     // K* slices of unit `nxt` into the other half of this CTA's store; iteration -1 only generates.
     const int64_t nit = (units - (int64_t)blockIdx.x + gridDim.x - 1) / gridDim.x;
+    // dbg bit 8 (256): where the MMA-issuing thread spends its cycles (printed by two CTAs at the end)
+    long long prof_full = 0, prof_acc = 0, prof_issue = 0, prof_gap = 0, prof_last = clock64();
+    const long long prof_t0 = prof_last;
     for (int64_t it = -1; it < nit; ++it) {
         const bool has_cur = it >= 0, has_nxt = it + 1 < nit;
         const int64_t ucur = (int64_t)blockIdx.x + it * gridDim.x, unxt = ucur + gridDim.x;
@@ -378,14 +383,21 @@ predict_i8_kernel(gpx_kernel_params kp, int n, int n128, int M, int S, const dou
                 const uint32_t iu1 = make_idesc(NT * 1, false), iu2 = make_idesc(NT * 2, false), iu3 = make_idesc(NT * 3, false),
                                iu4 = make_idesc(NT * 4, false), is4 = make_idesc(NT * 4, true);
                 int g = 0;
+                long long c0 = 0;
+                const long long u0 = clock64();
+                if (dbg & 256) prof_gap += u0 - prof_last;          // since the last commit of the previous unit
                 for (int rb = 0; rb < T; ++rb) {
                     if (rb > 0) {
+                        if (dbg & 256) c0 = clock64();
                         mbar_wait(b_accEmpty, (rb - 1) & 1);       // the epilogue has the planes in registers
+                        if (dbg & 256) prof_acc += clock64() - c0;
                         tc_fence_after();
                     }
                     for (int j = 0; j < 4 * (rb + 1); ++j, ++g) {
                         const int st = g % STAGES;
+                        if (dbg & 256) c0 = clock64();
                         mbar_wait(b_full + 8 * st, (g / STAGES) & 1);
+                        if (dbg & 256) { prof_full += clock64() - c0; c0 = clock64(); }
                         tc_fence_after();
                         if (!(dbg & 2)) {
                             const uint64_t a0 = descA0 + (uint64_t)(st * (STAGE_BYTES >> 4));
@@ -407,9 +419,11 @@ predict_i8_kernel(gpx_kernel_params kp, int n, int n128, int M, int S, const dou
                             mma_i8(tmem + 7 * NT, a0 + 7 * AS, b0 + 0 * BS, iu1, 1u);         // p = 7: plane 7
                         }
                         tc_commit(b_empty + 8 * st);        // frees the stage when these MMAs retire
+                        if (dbg & 256) prof_issue += clock64() - c0;
                     }
                     tc_commit(b_accFull);
                 }
+                if (dbg & 256) prof_last = clock64();
             }
         } else {
             // ---- generator (unit nxt) + epilogue (unit cur): warps 0..7, two per SM sub-partition --------
@@ -625,6 +639,12 @@ predict_i8_kernel(gpx_kernel_params kp, int n, int n128, int M, int S, const dou
             }
         }
         // the next iteration starts with a __syncthreads: sRed is free by the time it is written again
+    }
+    if ((dbg & 256) && t == GEN_WARPS * 32 && (blockIdx.x % 74) == 0) {
+        const double tot = (double)(clock64() - prof_t0);
+        printf("cta %d: %.0f cycles; MMA issuer: issuing %.1f%%, waiting for loads %.1f%%, for the epilogue %.1f%%, "
+               "between units (generator not done) %.1f%%\n", (int)blockIdx.x, tot, 100.0 * prof_issue / tot,
+               100.0 * prof_full / tot, 100.0 * prof_acc / tot, 100.0 * prof_gap / tot);
     }
     tc_fence_before();
     __syncthreads();
